@@ -1,0 +1,148 @@
+/*
+ * lwc_b200.h -- C ABI of the B200-native scoring hot path for llm-weighted-consensus.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types.  A Rust caller
+ * binds these symbols through `extern "C"` (rust/lwc-b200-sys) exactly where the reference
+ * crate computes the same quantities on the CPU; INTEGRATION.md shows the binding.
+ *
+ * What each entry point replaces in the reference (paths relative to /root/reference):
+ *
+ *   lwc_score_batch ........ the inline tally / normalise / voter-agreement block of
+ *                            score::completions::Client::create_streaming,
+ *                            src/score/completions/client.rs:384-456, batched over R
+ *                            requests, plus the embeddings-similarity stages that the
+ *                            training-table weight slot carries the data for
+ *                            (src/score/completions/weight.rs:15-18,66-74;
+ *                            src/embeddings/response.rs:4-24).  With
+ *                            similarity = LWC_SIM_IDENTITY it is the reference tally and
+ *                            nothing else.
+ *   lwc_merge_error_codes .. the all-votes-failed status merge, client.rs:386-409,459-463
+ *                            and src/score/completions/error.rs:41.
+ *   lwc_stage_f64 .......... the Vec<f64> -> device fp32 hop for
+ *                            embeddings::response::Embedding.embedding
+ *                            (src/embeddings/response.rs:19-24).
+ *
+ * Error convention mirrors error::ResponseError { code: u16, .. } (src/error.rs:8-13):
+ * every function returns 0 on success or an HTTP-style status -- 400 for a malformed
+ * argument (shape, null pointer, misalignment), 500 for a CUDA/NCCL failure, 503 when no
+ * usable device exists.  lwc_last_error_message() gives the text for the `message` field.
+ *
+ * Threading: a context may be used from many host threads; calls on one context are
+ * serialised internally.  Create one context per device.
+ */
+#ifndef LWC_B200_H
+#define LWC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LWC_OK 0
+#define LWC_ERR_INVALID 400
+#define LWC_ERR_INTERNAL 500
+#define LWC_ERR_UNAVAILABLE 503
+
+#define LWC_MAX_CHOICES 128 /* per-request candidates handled by lwc_score_batch */
+#define LWC_MAX_VOTERS 128  /* score::model: 1 <= LLMs <= 128, src/score/model/mod.rs:23-35 */
+
+typedef struct lwc_ctx lwc_ctx;
+
+typedef struct {
+    int32_t device;          /* CUDA ordinal this context drives */
+    int32_t chunk_requests;  /* host-memory calls are pipelined in chunks of this many requests; 0 = auto */
+    uint64_t reserved[4];
+} lwc_config;
+
+enum { LWC_SIM_IDENTITY = 0, /* S = I: the reference tally, client.rs:410-415 */
+       LWC_SIM_COSINE = 1 /* S = cosine similarity of the candidates' embeddings */ };
+
+enum { LWC_PREC_FP32 = 0,   /* fp32-grade result (confidences within 1e-5 relative); the Gram runs
+                               as error-compensated 3xTF32 on tensor cores or as fp32 FMA, by shape */
+       LWC_PREC_TF32X3 = 1, /* force the compensated tensor-core route */
+       LWC_PREC_TF32 = 2,   /* single-pass TF32 inputs, fp32 accumulate (confidences ~1e-3 relative) */
+       LWC_PREC_BF16 = 3 /* bf16 inputs, fp32 accumulate (pool path; confidences ~1e-2 relative) */ };
+
+enum { LWC_MEM_HOST = 0,  /* every pointer is host memory; the call returns with outputs written */
+       LWC_MEM_DEVICE = 1 /* every pointer is device memory on ctx's device; the call is
+                             asynchronous on `stream` */ };
+
+typedef struct {
+    int32_t R;             /* requests in the batch */
+    int32_t N;             /* candidate responses (choices) per request, 1..LWC_MAX_CHOICES (the
+                              reference itself requires >= 2, client.rs:115-120) */
+    int32_t D;             /* embedding dimension (ignored for LWC_SIM_IDENTITY) */
+    int32_t M;             /* voters (LLMs) per request, 0..LWC_MAX_VOTERS */
+    int32_t similarity;    /* LWC_SIM_* */
+    int32_t precision;     /* LWC_PREC_* */
+    int32_t memory;        /* LWC_MEM_* */
+    int32_t w_per_request; /* 1: w is [R][M]; 0: one [M] vector shared by all requests */
+} lwc_batch_desc;
+
+/* replaces: nothing (lifecycle).  Binds the context to cfg->device, creates its streams. */
+int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out);
+void lwc_ctx_destroy(lwc_ctx *ctx);
+/* Text of the last failure on this context (or of the last failed lwc_ctx_create when ctx is
+ * NULL); maps to ResponseError.message, src/error.rs:11. Never NULL. */
+const char *lwc_last_error_message(const lwc_ctx *ctx);
+/* Library / device identification: "lwc_b200 <version> sm_100a ..." */
+const char *lwc_version(void);
+
+/* Pinned host memory for the batch packer (the Rust host lays request embeddings out into
+ * one of these, contiguous [R][N][D]); freed with lwc_host_free. */
+int32_t lwc_host_alloc(lwc_ctx *ctx, size_t bytes, void **out);
+int32_t lwc_host_free(lwc_ctx *ctx, void *p);
+/* Plain device memory on the context's device, for callers that keep batches resident. */
+int32_t lwc_device_alloc(lwc_ctx *ctx, size_t bytes, void **out);
+int32_t lwc_device_free(lwc_ctx *ctx, void *p);
+/* Blocking copies for such callers (kind: 0 = host->device, 1 = device->host). */
+int32_t lwc_memcpy(lwc_ctx *ctx, void *dst, const void *src, size_t bytes, int32_t kind);
+/* The context's compute stream as a cudaStream_t (so a caller can record its own events on it). */
+void *lwc_ctx_stream(lwc_ctx *ctx);
+/* Waits for everything queued on `stream` (NULL = the context's own stream). */
+int32_t lwc_stream_synchronize(lwc_ctx *ctx, void *stream);
+
+/*
+ * Score a batch.  replaces client.rs:384-456 (see the table above).
+ *
+ *   E      [R][N][D] fp32, row-major, 16-byte aligned        (unused for LWC_SIM_IDENTITY)
+ *   V      [R][M][N] fp32 vote rows (Delta.vote, src/score/completions/response.rs:189);
+ *          a voter without a vote (vote == None, client.rs:410) is a row whose FIRST element
+ *          is NaN
+ *   w      [R][M] or [M] fp32 voter weights (choice.weight); NaN = None -> 0
+ *          (unwrap_or(ZERO), client.rs:412-413)
+ *   conf   [R][N] confidence  = cw / sum(cw) if sum > 0 else 0      (client.rs:428-437)
+ *   cw     [R][N] choice weight                                     (client.rs:410-415)
+ *   agree  [R][M] voter confidence sum_i conf_i * V_mi; NaN for absent voters
+ *                                                                  (client.rs:438-449)
+ *   winner [R]    argmax_j conf_j, ties -> lowest j, -1 when sum(cw) is not > 0
+ *   rank   [R][N] choice indices by confidence, descending, stable
+ * Any output pointer may be NULL.  `stream` is a cudaStream_t (NULL = the context's stream)
+ * and is honoured for LWC_MEM_DEVICE; LWC_MEM_HOST calls run on the context's own streams,
+ * chunked so that host->device copies overlap the kernels, and return when outputs are home.
+ */
+int32_t lwc_score_batch(lwc_ctx *ctx, const lwc_batch_desc *desc, const float *E, const float *V,
+                        const float *w, float *conf, float *cw, float *agree, int32_t *winner,
+                        int32_t *rank, void *stream);
+
+/* Name of the kernel lwc_score_batch would launch for this descriptor ("small16_tf32x3", ...);
+ * empty string for an invalid descriptor.  For logs, tests and the bench's roofline record. */
+const char *lwc_kernel_for(const lwc_ctx *ctx, const lwc_batch_desc *desc);
+
+/* Number of kernels this library has launched on behalf of ctx since creation. */
+uint64_t lwc_launch_count(const lwc_ctx *ctx);
+
+/* replaces: client.rs:386-409,459-463.  codes[m] = 0 for a voter without an error, else its
+ * status code.  Returns 0 if any voter succeeded, else the status AllVotesFailed maps to. */
+int32_t lwc_merge_error_codes(const uint16_t *codes, int32_t n_voters);
+
+/* replaces: the f64 -> fp32 hop for Embedding.embedding (embeddings/response.rs:21).
+ * Converts n doubles at src (host) to floats at dst (host, typically from lwc_host_alloc). */
+int32_t lwc_stage_f64(lwc_ctx *ctx, const double *src, size_t n, float *dst);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LWC_B200_H */

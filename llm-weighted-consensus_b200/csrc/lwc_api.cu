@@ -1,0 +1,463 @@
+// lwc_api.cu -- the C ABI (include/lwc_b200.h) over the sm_100a scoring kernels.
+// Host side: context + streams, shape validation, kernel routing, and the chunked
+// host-memory pipeline (H2D on a copy stream overlapped with kernels on the compute stream).
+// There is no CPU fallback anywhere in this file: without a CUDA device every entry point
+// that computes returns 503/500.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+
+#include "../../include/lwc_b200.h"
+#include "score_generic.cuh"
+#include "score_small.cuh"
+
+#define LWC_VERSION_STRING "lwc_b200 0.1.0 (sm_100a)"
+
+namespace {
+
+std::mutex g_err_mu;
+std::string g_create_err = "";
+
+struct Slot {
+    void *buf[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t cap[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    cudaEvent_t h2d_done = nullptr; // inputs of this slot are on the device
+    cudaEvent_t all_done = nullptr; // kernel + D2H of this slot finished (slot reusable)
+    bool used = false;
+};
+
+} // namespace
+
+struct lwc_ctx {
+    int device = 0;
+    int sm_count = 0;
+    int chunk_requests = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    std::mutex mu;
+    std::string err;
+    uint64_t launches = 0;
+    Slot slots[2];
+    int small_kw = 4; // warps per request in the small-pool kernel (LWC_SMALL_KW)
+    int small_u = 0;  // k-chunks in flight per lane, 0 = per-shape default (LWC_SMALL_U)
+};
+
+namespace {
+
+int fail(lwc_ctx *ctx, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) {
+        ctx->err = buf;
+    } else {
+        std::lock_guard<std::mutex> lk(g_err_mu);
+        g_create_err = buf;
+    }
+    return code;
+}
+
+#define CUDA_TRY(ctx, expr)                                                                              \
+    do {                                                                                                 \
+        cudaError_t _e = (expr);                                                                         \
+        if (_e != cudaSuccess)                                                                           \
+            return fail((ctx), LWC_ERR_INTERNAL, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                        __FILE__, __LINE__);                                                             \
+    } while (0)
+
+enum Route { ROUTE_INVALID = 0, ROUTE_GENERIC, ROUTE_SMALL };
+
+struct Plan {
+    Route route = ROUTE_INVALID;
+    int np = 0;      // padded pool size
+    bool x3 = true;  // small route: compensated 3xTF32
+    const char *name = "";
+};
+
+Plan plan_for(const lwc_batch_desc &d, const void *E) {
+    Plan pl;
+    if (d.R < 0 || d.N < 1 || d.N > LWC_MAX_CHOICES || d.M < 0 || d.M > LWC_MAX_VOTERS) return pl;
+    if (d.similarity != LWC_SIM_IDENTITY && d.similarity != LWC_SIM_COSINE) return pl;
+    if (d.precision < LWC_PREC_FP32 || d.precision > LWC_PREC_BF16) return pl;
+    if (d.memory != LWC_MEM_HOST && d.memory != LWC_MEM_DEVICE) return pl;
+    if (d.similarity == LWC_SIM_COSINE && d.D < 1) return pl;
+    const int np = d.N <= 32 ? 32 : (d.N <= 64 ? 64 : 128);
+    if (d.similarity == LWC_SIM_IDENTITY) {
+        pl.route = ROUTE_GENERIC;
+        pl.np = np;
+        pl.name = "tally";
+        return pl;
+    }
+    const bool aligned = (d.D % 4 == 0) && ((reinterpret_cast<uintptr_t>(E) & 15u) == 0);
+    if (d.N <= 32 && aligned) {
+        pl.route = ROUTE_SMALL;
+        pl.np = d.N <= 16 ? 16 : 32;
+        pl.x3 = (d.precision == LWC_PREC_FP32 || d.precision == LWC_PREC_TF32X3);
+        pl.name = pl.np == 16 ? (pl.x3 ? "small16_tf32x3" : "small16_tf32") : (pl.x3 ? "small32_tf32x3" : "small32_tf32");
+        return pl;
+    }
+    pl.route = ROUTE_GENERIC;
+    pl.np = np;
+    pl.name = np == 32 ? "generic32_fp32" : (np == 64 ? "generic64_fp32" : "generic128_fp32");
+    return pl;
+}
+
+template <int NP>
+cudaError_t launch_generic(const lwc::ScoreParams &p, cudaStream_t st) {
+    using C = lwc::GenericCfg<NP>;
+    static bool configured[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_generic_kernel<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)C::smem_bytes());
+        if (e != cudaSuccess) return e;
+        configured[dev & 63] = true;
+    }
+    lwc::score_generic_kernel<NP><<<p.R, lwc::kGenThreads, C::smem_bytes(), st>>>(p);
+    return cudaGetLastError();
+}
+
+template <int NT, bool X3, int KW, int U>
+cudaError_t launch_small_one(const lwc::ScoreParams &p, cudaStream_t st) {
+    using C = lwc::SmallCfg<NT, X3, KW, U>;
+    static bool configured[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_small_kernel<NT, X3, KW, U>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem_bytes());
+        if (e != cudaSuccess) return e;
+        configured[dev & 63] = true;
+    }
+    lwc::score_small_kernel<NT, X3, KW, U><<<p.R, KW * 32, C::smem_bytes(), st>>>(p);
+    return cudaGetLastError();
+}
+
+template <int NT, bool X3>
+cudaError_t launch_small(const lwc::ScoreParams &p, cudaStream_t st, int kw, int u) {
+    if (u == 0) u = (NT == 16) ? 4 : 2;
+    const int key = kw * 10 + u;
+    switch (key) {
+        case 22: return launch_small_one<NT, X3, 2, 2>(p, st);
+        case 24: return launch_small_one<NT, X3, 2, 4>(p, st);
+        case 42: return launch_small_one<NT, X3, 4, 2>(p, st);
+        case 44: return launch_small_one<NT, X3, 4, 4>(p, st);
+        case 82: return launch_small_one<NT, X3, 8, 2>(p, st);
+        case 84: return launch_small_one<NT, X3, 8, 4>(p, st);
+        default: return launch_small_one<NT, X3, 4, 2>(p, st);
+    }
+}
+
+int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStream_t st) {
+    if (p.R == 0) return LWC_OK;
+    cudaError_t e = cudaSuccess;
+    if (pl.route == ROUTE_SMALL) {
+        if (pl.np == 16)
+            e = pl.x3 ? launch_small<16, true>(p, st, ctx->small_kw, ctx->small_u)
+                      : launch_small<16, false>(p, st, ctx->small_kw, ctx->small_u);
+        else
+            e = pl.x3 ? launch_small<32, true>(p, st, ctx->small_kw, ctx->small_u)
+                      : launch_small<32, false>(p, st, ctx->small_kw, ctx->small_u);
+    } else {
+        if (pl.np == 32)
+            e = launch_generic<32>(p, st);
+        else if (pl.np == 64)
+            e = launch_generic<64>(p, st);
+        else
+            e = launch_generic<128>(p, st);
+    }
+    if (e != cudaSuccess) return fail(ctx, LWC_ERR_INTERNAL, "kernel launch (%s) failed: %s", pl.name, cudaGetErrorString(e));
+    ctx->launches++;
+    return LWC_OK;
+}
+
+int ensure(lwc_ctx *ctx, Slot &s, int which, size_t bytes) {
+    if (bytes <= s.cap[which]) return LWC_OK;
+    if (s.buf[which]) CUDA_TRY(ctx, cudaFree(s.buf[which]));
+    s.buf[which] = nullptr;
+    s.cap[which] = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    CUDA_TRY(ctx, cudaMalloc(&s.buf[which], want));
+    s.cap[which] = want;
+    return LWC_OK;
+}
+
+int score_host(lwc_ctx *ctx, const lwc_batch_desc &d, const Plan &pl, const float *E, const float *V, const float *w,
+               float *conf, float *cw, float *agree, int32_t *winner, int32_t *rank) {
+    const bool cosine = d.similarity == LWC_SIM_COSINE;
+    const size_t e_req = cosine ? (size_t)d.N * d.D * sizeof(float) : 0;
+    const size_t v_req = (size_t)d.M * d.N * sizeof(float);
+    int chunk = ctx->chunk_requests;
+    if (chunk <= 0) {
+        // ~32 MiB of embeddings per chunk: large enough for PCIe efficiency, small enough to overlap
+        size_t per = e_req + v_req + 64;
+        chunk = (int)((32u << 20) / per);
+        if (chunk < 1) chunk = 1;
+    }
+    if (chunk > d.R) chunk = d.R;
+    // the shared weight vector (w_per_request == 0) is uploaded once into slot 0's w buffer
+    const float *dw_shared = nullptr;
+    if (!d.w_per_request && d.M > 0) {
+        int rc = ensure(ctx, ctx->slots[0], 7, (size_t)d.M * sizeof(float));
+        if (rc) return rc;
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->slots[0].buf[7], w, (size_t)d.M * sizeof(float), cudaMemcpyHostToDevice,
+                                      ctx->stream));
+        dw_shared = static_cast<const float *>(ctx->slots[0].buf[7]);
+    }
+    int ci = 0;
+    for (int r0 = 0; r0 < d.R; r0 += chunk, ++ci) {
+        const int rc_n = (d.R - r0 < chunk) ? d.R - r0 : chunk;
+        Slot &s = ctx->slots[ci & 1];
+        int rc;
+        // a slot may be refilled only after its previous kernel and D2H finished
+        if (s.used) CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copy_stream, s.all_done, 0));
+        // (re)allocation happens only while growing; cudaFree synchronises, which is safe here
+        if ((rc = ensure(ctx, s, 0, e_req * rc_n))) return rc;
+        if ((rc = ensure(ctx, s, 1, v_req * rc_n))) return rc;
+        if ((rc = ensure(ctx, s, 2, (size_t)d.M * rc_n * sizeof(float)))) return rc;
+        if ((rc = ensure(ctx, s, 3, (size_t)d.N * rc_n * sizeof(float) * 2))) return rc;             // conf | cw
+        if ((rc = ensure(ctx, s, 4, (size_t)d.M * rc_n * sizeof(float)))) return rc;                 // agree
+        if ((rc = ensure(ctx, s, 5, (size_t)rc_n * sizeof(int32_t) * ((size_t)d.N + 1)))) return rc; // winner | rank
+        if (cosine)
+            CUDA_TRY(ctx, cudaMemcpyAsync(s.buf[0], E + (size_t)r0 * d.N * d.D, e_req * rc_n, cudaMemcpyHostToDevice,
+                                          ctx->copy_stream));
+        if (v_req)
+            CUDA_TRY(ctx, cudaMemcpyAsync(s.buf[1], V + (size_t)r0 * d.M * d.N, v_req * rc_n, cudaMemcpyHostToDevice,
+                                          ctx->copy_stream));
+        if (d.w_per_request && d.M > 0)
+            CUDA_TRY(ctx, cudaMemcpyAsync(s.buf[2], w + (size_t)r0 * d.M, (size_t)d.M * rc_n * sizeof(float),
+                                          cudaMemcpyHostToDevice, ctx->copy_stream));
+        CUDA_TRY(ctx, cudaEventRecord(s.h2d_done, ctx->copy_stream));
+        CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, s.h2d_done, 0));
+
+        lwc::ScoreParams p;
+        p.E = static_cast<const float *>(s.buf[0]);
+        p.V = static_cast<const float *>(s.buf[1]);
+        p.w = d.w_per_request ? static_cast<const float *>(s.buf[2]) : dw_shared;
+        float *dconf = static_cast<float *>(s.buf[3]);
+        float *dcw = dconf + (size_t)d.N * rc_n;
+        int32_t *dwin = static_cast<int32_t *>(s.buf[5]);
+        int32_t *drank = dwin + rc_n;
+        p.conf = conf ? dconf : nullptr;
+        p.cw = cw ? dcw : nullptr;
+        p.agree = agree ? static_cast<float *>(s.buf[4]) : nullptr;
+        p.winner = winner ? dwin : nullptr;
+        p.rank = rank ? drank : nullptr;
+        p.R = rc_n, p.N = d.N, p.D = d.D, p.M = d.M;
+        p.w_per_request = d.w_per_request;
+        p.cosine = cosine ? 1 : 0;
+        if ((rc = launch_plan(ctx, pl, p, ctx->stream))) return rc;
+
+        if (conf)
+            CUDA_TRY(ctx, cudaMemcpyAsync(conf + (size_t)r0 * d.N, dconf, (size_t)d.N * rc_n * sizeof(float),
+                                          cudaMemcpyDeviceToHost, ctx->stream));
+        if (cw)
+            CUDA_TRY(ctx, cudaMemcpyAsync(cw + (size_t)r0 * d.N, dcw, (size_t)d.N * rc_n * sizeof(float),
+                                          cudaMemcpyDeviceToHost, ctx->stream));
+        if (agree && d.M > 0)
+            CUDA_TRY(ctx, cudaMemcpyAsync(agree + (size_t)r0 * d.M, s.buf[4], (size_t)d.M * rc_n * sizeof(float),
+                                          cudaMemcpyDeviceToHost, ctx->stream));
+        if (winner)
+            CUDA_TRY(ctx, cudaMemcpyAsync(winner + r0, dwin, (size_t)rc_n * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                                          ctx->stream));
+        if (rank)
+            CUDA_TRY(ctx, cudaMemcpyAsync(rank + (size_t)r0 * d.N, drank, (size_t)d.N * rc_n * sizeof(int32_t),
+                                          cudaMemcpyDeviceToHost, ctx->stream));
+        CUDA_TRY(ctx, cudaEventRecord(s.all_done, ctx->stream));
+        s.used = true;
+    }
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return LWC_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *lwc_version(void) { return LWC_VERSION_STRING; }
+
+const char *lwc_last_error_message(const lwc_ctx *ctx) {
+    if (ctx) return ctx->err.c_str();
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    static thread_local std::string copy;
+    copy = g_create_err;
+    return copy.c_str();
+}
+
+int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
+    if (!out) return fail(nullptr, LWC_ERR_INVALID, "lwc_ctx_create: out is NULL");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, LWC_ERR_UNAVAILABLE, "no CUDA device: %s (this library has no CPU path)",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    const int dev = cfg ? cfg->device : 0;
+    if (dev < 0 || dev >= ndev) return fail(nullptr, LWC_ERR_INVALID, "device %d out of range (0..%d)", dev, ndev - 1);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, dev)) != cudaSuccess)
+        return fail(nullptr, LWC_ERR_INTERNAL, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
+    if (prop.major != 10)
+        return fail(nullptr, LWC_ERR_UNAVAILABLE, "device %d is sm_%d%d; this library carries sm_100a code only", dev,
+                    prop.major, prop.minor);
+    lwc_ctx *ctx = new lwc_ctx();
+    ctx->device = dev;
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->chunk_requests = cfg ? cfg->chunk_requests : 0;
+    if (const char *s = getenv("LWC_SMALL_KW")) ctx->small_kw = atoi(s);
+    if (const char *s = getenv("LWC_SMALL_U")) ctx->small_u = atoi(s);
+    if (ctx->small_kw != 2 && ctx->small_kw != 4 && ctx->small_kw != 8) ctx->small_kw = 4;
+    if (ctx->small_u != 0 && ctx->small_u != 2 && ctx->small_u != 4) ctx->small_u = 0;
+    bool ok = cudaSetDevice(dev) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; ok && i < 2; ++i)
+        ok = cudaEventCreateWithFlags(&ctx->slots[i].h2d_done, cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&ctx->slots[i].all_done, cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) {
+        int rc = fail(nullptr, LWC_ERR_INTERNAL, "context setup failed: %s", cudaGetErrorString(cudaGetLastError()));
+        delete ctx;
+        return rc;
+    }
+    *out = ctx;
+    return LWC_OK;
+}
+
+void lwc_ctx_destroy(lwc_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+    for (auto &s : ctx->slots) {
+        for (auto &b : s.buf)
+            if (b) cudaFree(b);
+        if (s.h2d_done) cudaEventDestroy(s.h2d_done);
+        if (s.all_done) cudaEventDestroy(s.all_done);
+    }
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    delete ctx;
+}
+
+int32_t lwc_host_alloc(lwc_ctx *ctx, size_t bytes, void **out) {
+    if (!ctx || !out) return fail(ctx, LWC_ERR_INVALID, "lwc_host_alloc: NULL argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+    return LWC_OK;
+}
+
+int32_t lwc_host_free(lwc_ctx *ctx, void *p) {
+    if (!ctx) return LWC_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (p) CUDA_TRY(ctx, cudaFreeHost(p));
+    return LWC_OK;
+}
+
+int32_t lwc_device_alloc(lwc_ctx *ctx, size_t bytes, void **out) {
+    if (!ctx || !out) return fail(ctx, LWC_ERR_INVALID, "lwc_device_alloc: NULL argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaMalloc(out, bytes ? bytes : 1));
+    return LWC_OK;
+}
+
+int32_t lwc_device_free(lwc_ctx *ctx, void *p) {
+    if (!ctx) return LWC_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    if (p) CUDA_TRY(ctx, cudaFree(p));
+    return LWC_OK;
+}
+
+int32_t lwc_memcpy(lwc_ctx *ctx, void *dst, const void *src, size_t bytes, int32_t kind) {
+    if (!ctx || (bytes && (!dst || !src))) return fail(ctx, LWC_ERR_INVALID, "lwc_memcpy: NULL argument");
+    if (kind != 0 && kind != 1) return fail(ctx, LWC_ERR_INVALID, "lwc_memcpy: kind must be 0 (H2D) or 1 (D2H)");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, bytes, kind == 0 ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return LWC_OK;
+}
+
+void *lwc_ctx_stream(lwc_ctx *ctx) { return ctx ? static_cast<void *>(ctx->stream) : nullptr; }
+
+int32_t lwc_stream_synchronize(lwc_ctx *ctx, void *stream) {
+    if (!ctx) return LWC_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaStreamSynchronize(stream ? static_cast<cudaStream_t>(stream) : ctx->stream));
+    return LWC_OK;
+}
+
+const char *lwc_kernel_for(const lwc_ctx *ctx, const lwc_batch_desc *desc) {
+    (void)ctx;
+    if (!desc) return "";
+    // alignment is unknown here: assume the documented 16-byte alignment of E
+    return plan_for(*desc, nullptr).name;
+}
+
+uint64_t lwc_launch_count(const lwc_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int32_t lwc_score_batch(lwc_ctx *ctx, const lwc_batch_desc *desc, const float *E, const float *V, const float *w,
+                        float *conf, float *cw, float *agree, int32_t *winner, int32_t *rank, void *stream) {
+    if (!ctx) return LWC_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!desc) return fail(ctx, LWC_ERR_INVALID, "lwc_score_batch: desc is NULL");
+    const lwc_batch_desc d = *desc;
+    const Plan pl = plan_for(d, E);
+    if (pl.route == ROUTE_INVALID)
+        return fail(ctx, LWC_ERR_INVALID,
+                    "lwc_score_batch: invalid descriptor (R=%d N=%d D=%d M=%d sim=%d prec=%d mem=%d); need R>=0, "
+                    "1<=N<=%d, 0<=M<=%d, D>=1 for cosine",
+                    d.R, d.N, d.D, d.M, d.similarity, d.precision, d.memory, LWC_MAX_CHOICES, LWC_MAX_VOTERS);
+    if (d.R == 0) return LWC_OK;
+    if (d.similarity == LWC_SIM_COSINE && !E) return fail(ctx, LWC_ERR_INVALID, "lwc_score_batch: E is NULL");
+    if (d.M > 0 && (!V || !w)) return fail(ctx, LWC_ERR_INVALID, "lwc_score_batch: V or w is NULL with M > 0");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    if (d.memory == LWC_MEM_HOST) return score_host(ctx, d, pl, E, V, w, conf, cw, agree, winner, rank);
+
+    lwc::ScoreParams p;
+    p.E = E, p.V = V, p.w = w;
+    p.conf = conf, p.cw = cw, p.agree = agree, p.winner = winner, p.rank = rank;
+    p.R = d.R, p.N = d.N, p.D = d.D, p.M = d.M;
+    p.w_per_request = d.w_per_request;
+    p.cosine = d.similarity == LWC_SIM_COSINE ? 1 : 0;
+    return launch_plan(ctx, pl, p, stream ? static_cast<cudaStream_t>(stream) : ctx->stream);
+}
+
+int32_t lwc_merge_error_codes(const uint16_t *codes, int32_t n_voters) {
+    // client.rs:386-409: only while every voter so far has errored does the merge continue.
+    bool have = false;
+    uint16_t merged = 0;
+    for (int32_t m = 0; m < n_voters; ++m) {
+        const uint16_t e = codes[m];
+        if (e == 0) return 0; // a voter without an error: not an all-failed request
+        if (!have) {
+            merged = e;
+            have = true;
+        } else if (e != merged) {
+            const bool both_4xx = e >= 400 && e < 500 && merged >= 400 && merged < 500;
+            merged = both_4xx ? 400 : 500;
+        }
+    }
+    return have ? merged : 500; // AllVotesFailed(None) -> 500 (score/completions/error.rs:41)
+}
+
+int32_t lwc_stage_f64(lwc_ctx *ctx, const double *src, size_t n, float *dst) {
+    if (n && (!src || !dst)) return fail(ctx, LWC_ERR_INVALID, "lwc_stage_f64: NULL argument");
+    for (size_t i = 0; i < n; ++i) dst[i] = static_cast<float>(src[i]);
+    return LWC_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,129 @@
+// score_common.cuh -- shared device-side pieces of the scoring kernels (sm_100a).
+//
+// Everything after the similarity matrix is the reference's tally, restated per request:
+//   t_i   = sum_m w_m V_mi            src/score/completions/client.rs:410-415
+//   sum   = sum_j cw_j                client.rs:422-424
+//   conf  = cw / sum if sum > 0       client.rs:428-437
+//   agree = sum_i conf_i V_mi         client.rs:438-449
+// with cw = t (similarity identity, the reference) or cw_j = sum_i t_i S_ij (cosine,
+// build-defined).  winner / rank are build-defined (8.0 step 6).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace lwc {
+
+struct ScoreParams {
+    const float *E;  // [R][N][D]
+    const float *V;  // [R][M][N]
+    const float *w;  // [R][M] or [M]
+    float *conf;     // [R][N]
+    float *cw;       // [R][N]
+    float *agree;    // [R][M]
+    int32_t *winner; // [R]
+    int32_t *rank;   // [R][N]
+    int R, N, D, M;
+    int w_per_request;
+    int cosine;
+};
+
+constexpr unsigned kFullMask = 0xffffffffu;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
+    return v;
+}
+
+// (value, index) arg-max with ties resolved to the lowest index.
+__device__ __forceinline__ void warp_argmax(float &v, int &idx) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        float ov = __shfl_xor_sync(kFullMask, v, o);
+        int oi = __shfl_xor_sync(kFullMask, idx, o);
+        if (ov > v || (ov == v && oi < idx)) {
+            v = ov;
+            idx = oi;
+        }
+    }
+}
+
+// 128-bit streaming load: read-only path, no L1 allocation (every byte of E is used once).
+__device__ __forceinline__ float4 ld_stream_f4(const float *p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+// Warp-wide tail of the path for one request whose candidates fit one warp (N <= 32):
+// lane j owns choice j.  S is the raw Gram matrix E E^T in shared memory (pitch `pitch`),
+// ignored when !p.cosine.
+__device__ __forceinline__ void warp_tally_and_rank(const ScoreParams &p, int r, const float *S, int pitch,
+                                                    int lane) {
+    const int N = p.N, M = p.M;
+    const float *Vr = p.V + (size_t)r * M * N;
+    const float *wr = p.w + (p.w_per_request ? (size_t)r * M : 0);
+    const bool act = lane < N;
+
+    float t = 0.f;
+    for (int m = 0; m < M; ++m) {
+        const float v0 = __ldg(Vr + (size_t)m * N);
+        if (isnan(v0)) continue; // voter without a vote (client.rs:410) -- warp-uniform
+        float wm = __ldg(wr + m);
+        if (isnan(wm)) wm = 0.f; // weight None -> 0 (client.rs:412-413)
+        if (act) t = fmaf(__ldg(Vr + (size_t)m * N + lane), wm, t);
+    }
+
+    float c = t;
+    if (p.cosine) {
+        const float d = act ? S[lane * pitch + lane] : 0.f;
+        const float rn = d > 0.f ? 1.0f / sqrtf(d) : 0.f; // zero-norm row: E^_i = 0
+        const float u = t * rn;
+        float acc = 0.f;
+        for (int i = 0; i < N; ++i) {
+            const float ui = __shfl_sync(kFullMask, u, i);
+            if (act) acc = fmaf(ui, S[i * pitch + lane], acc);
+        }
+        c = acc * rn;
+    }
+    if (!act) c = 0.f;
+    const float sum = warp_sum(c);
+    const bool positive = sum > 0.f;
+    const float cf = (positive && act) ? c / sum : 0.f;
+
+    if (act) {
+        if (p.cw) p.cw[(size_t)r * N + lane] = c;
+        if (p.conf) p.conf[(size_t)r * N + lane] = cf;
+    }
+    if (p.winner) {
+        float bv = act ? cf : -1.f;
+        int bi = act ? lane : 0x7fffffff;
+        warp_argmax(bv, bi);
+        if (lane == 0) p.winner[r] = positive ? bi : -1;
+    }
+    if (p.rank) {
+        int pos = 0;
+        for (int i = 0; i < N; ++i) {
+            const float ci = __shfl_sync(kFullMask, cf, i);
+            pos += (ci > cf || (ci == cf && i < lane)) ? 1 : 0;
+        }
+        if (act) p.rank[(size_t)r * N + pos] = lane;
+    }
+    if (p.agree) {
+        for (int m = 0; m < M; ++m) {
+            const float v0 = __ldg(Vr + (size_t)m * N);
+            float a;
+            if (isnan(v0)) {
+                a = __int_as_float(0x7fc00000);
+            } else {
+                a = warp_sum(act ? cf * __ldg(Vr + (size_t)m * N + lane) : 0.f);
+            }
+            if (lane == 0) p.agree[(size_t)r * M + m] = a;
+        }
+    }
+}
+
+} // namespace lwc

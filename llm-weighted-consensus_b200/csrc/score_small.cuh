@@ -1,0 +1,211 @@
+// score_small.cuh -- fused normalise + similarity + vote kernel for small pools (N <= 32).
+//
+// One CTA per request; its KW warps split the embedding dimension.  Every byte of the
+// request's [N][D] fp32 tile is read from HBM exactly once, straight into registers with
+// 128-bit loads laid out so that the loaded registers ARE the tensor-core fragments:
+// in mma.m16n8k8 lane (g = lane/4, t = lane%4) holds A[g][t], A[g+8][t], A[g][t+4],
+// A[g+8][t+4] and B[t][g], B[t+4][g].  For a Gram matrix B = A^T, so the float4 a lane loads
+// from row g at k0+4t feeds both operands; no shared memory, no transposes.  (The k order
+// inside a 16-wide chunk is permuted identically for A and B, which a dot product ignores.)
+//
+// fp32-grade accuracy on tensor cores: x = hi + lo with hi = tf32(x), lo = tf32(x - hi);
+//   S ~= hi.hi^T + hi.lo^T + (hi.lo^T)^T        (the lo.lo^T term is < 2^-22 relative)
+// so only two MMA streams are needed (HH and HL); HL^T is formed in the epilogue.
+//
+// Bound: HBM.  Algorithmic bytes/request = 4ND + 4MN + 4M + 12N + 4M + 4.
+#pragma once
+
+#include "score_common.cuh"
+
+namespace lwc {
+
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return r;
+}
+
+__device__ __forceinline__ void mma_m16n8k8_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                                 uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// NT: padded pool size (16 or 32).  X3: error-compensated 3xTF32 (true) or single TF32 (false).
+// KW: warps per CTA (= K-split factor).  U: 16-wide k-chunks in flight per lane.
+template <int NT, bool X3, int KW, int U>
+struct SmallCfg {
+    static constexpr int RPL = NT / 8;  // rows per lane
+    static constexpr int MT = NT / 16;  // 16-row MMA tiles
+    static constexpr int NTL = NT / 8;  // 8-col MMA tiles
+    static constexpr int PITCH = NT + 1;
+    // fragment registers per lane that cross warps in the K-split reduction
+    static constexpr int NACC = (MT * NTL + (X3 ? MT * NTL : 0)) * 4;
+    static constexpr size_t smem_bytes() {
+        size_t red = (size_t)(KW - 1) * NACC * 32 * sizeof(float);
+        size_t tile = (size_t)NT * PITCH * sizeof(float);
+        return red + tile;
+    }
+};
+
+template <int NT, bool X3, int KW, int U>
+__global__ void __launch_bounds__(KW * 32, (NT == 16 ? 32 : 16) / KW)
+score_small_kernel(const ScoreParams p) {
+    using C = SmallCfg<NT, X3, KW, U>;
+    constexpr int RPL = C::RPL, MT = C::MT, NTL = C::NTL, PITCH = C::PITCH;
+    extern __shared__ __align__(16) float smem[];
+    float *red = smem;                                    // [KW-1][NACC][32]
+    float *tile = smem + (size_t)(KW - 1) * C::NACC * 32; // [NT][PITCH]
+
+    const int r = blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int N = p.N, D = p.D;
+
+    float hh[MT][NTL][4];
+    float hl[MT][NTL][4];
+#pragma unroll
+    for (int a = 0; a < MT; ++a)
+#pragma unroll
+        for (int b = 0; b < NTL; ++b)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) hh[a][b][e] = hl[a][b][e] = 0.f;
+
+    if (p.cosine) {
+        const float *Er = p.E + (size_t)r * N * D;
+        const float *rowp[RPL];
+        bool rv[RPL];
+#pragma unroll
+        for (int q = 0; q < RPL; ++q) {
+            const int row = g + 8 * q;
+            rv[q] = row < N;
+            rowp[q] = Er + (size_t)(rv[q] ? row : 0) * D + 4 * t;
+        }
+        // 16-wide chunks, dealt round-robin in groups of U to the KW warps
+        const int nchunk = (D + 15) >> 4;
+        for (int c0 = warp * U; c0 < nchunk; c0 += KW * U) {
+            float4 buf[U][RPL];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int k = (c0 + u) * 16 + 4 * t;
+#pragma unroll
+                for (int q = 0; q < RPL; ++q) {
+                    if (rv[q] && k < D)
+                        buf[u][q] = ld_stream_f4(rowp[q] + (size_t)(c0 + u) * 16);
+                    else
+                        buf[u][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t xh[RPL], yh[RPL], xl[RPL], yl[RPL];
+#pragma unroll
+                    for (int q = 0; q < RPL; ++q) {
+                        const float x = h ? buf[u][q].z : buf[u][q].x;
+                        const float y = h ? buf[u][q].w : buf[u][q].y;
+                        xh[q] = to_tf32(x);
+                        yh[q] = to_tf32(y);
+                        if (X3) {
+                            xl[q] = to_tf32(x - __uint_as_float(xh[q]));
+                            yl[q] = to_tf32(y - __uint_as_float(yh[q]));
+                        }
+                    }
+#pragma unroll
+                    for (int a = 0; a < MT; ++a) {
+#pragma unroll
+                        for (int b = 0; b < NTL; ++b) {
+                            if (b >= 2 * a) // upper blocks only: S is symmetric
+                                mma_m16n8k8_tf32(hh[a][b], xh[2 * a], xh[2 * a + 1], yh[2 * a], yh[2 * a + 1], xh[b],
+                                                 yh[b]);
+                            if (X3)
+                                mma_m16n8k8_tf32(hl[a][b], xh[2 * a], xh[2 * a + 1], yh[2 * a], yh[2 * a + 1], xl[b],
+                                                 yl[b]);
+                        }
+                    }
+                }
+            }
+        }
+
+        // ---- K-split reduction: warps 1..KW-1 park their fragments, warp 0 adds them in order
+        if (KW > 1) {
+            if (warp > 0) {
+                float *dst = red + (size_t)(warp - 1) * C::NACC * 32 + lane;
+                int s = 0;
+#pragma unroll
+                for (int a = 0; a < MT; ++a)
+#pragma unroll
+                    for (int b = 0; b < NTL; ++b)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            dst[(s++) * 32] = hh[a][b][e];
+                            if (X3) dst[(s++) * 32] = hl[a][b][e];
+                        }
+            }
+            __syncthreads();
+            if (warp == 0) {
+                for (int wsrc = 0; wsrc < KW - 1; ++wsrc) {
+                    const float *src = red + (size_t)wsrc * C::NACC * 32 + lane;
+                    int s = 0;
+#pragma unroll
+                    for (int a = 0; a < MT; ++a)
+#pragma unroll
+                        for (int b = 0; b < NTL; ++b)
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                hh[a][b][e] += src[(s++) * 32];
+                                if (X3) hl[a][b][e] += src[(s++) * 32];
+                            }
+                }
+            }
+        }
+        if (warp != 0) return;
+
+        // ---- assemble S = HH + (HL + HL^T) in the shared tile (fragment (a,b,e) -> (row,col))
+        if (X3) {
+#pragma unroll
+            for (int a = 0; a < MT; ++a)
+#pragma unroll
+                for (int b = 0; b < NTL; ++b)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int row = 16 * a + g + 8 * (e >> 1), col = 8 * b + 2 * t + (e & 1);
+                        tile[row * PITCH + col] = hl[a][b][e];
+                    }
+            __syncwarp();
+#pragma unroll
+            for (int a = 0; a < MT; ++a)
+#pragma unroll
+                for (int b = 0; b < NTL; ++b)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int row = 16 * a + g + 8 * (e >> 1), col = 8 * b + 2 * t + (e & 1);
+                        if (b >= 2 * a) hh[a][b][e] += hl[a][b][e] + tile[col * PITCH + row];
+                    }
+            __syncwarp();
+        }
+#pragma unroll
+        for (int a = 0; a < MT; ++a)
+#pragma unroll
+            for (int b = 0; b < NTL; ++b)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int row = 16 * a + g + 8 * (e >> 1), col = 8 * b + 2 * t + (e & 1);
+                    if (b >= 2 * a) {
+                        tile[row * PITCH + col] = hh[a][b][e];
+                        if (b >= 2 * a + 2) tile[col * PITCH + row] = hh[a][b][e]; // mirror the off-diagonal block
+                    }
+                }
+        __syncwarp();
+    } else if (warp != 0) {
+        return;
+    }
+
+    warp_tally_and_rank(p, r, tile, PITCH, lane);
+}
+
+} // namespace lwc

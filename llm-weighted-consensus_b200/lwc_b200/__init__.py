@@ -1,0 +1,251 @@
+"""ctypes binding of the C ABI in include/lwc_b200.h (liblwc_b200.so).
+
+This is a thin test/bench harness over the drop-in boundary; the product is the shared
+library.  There is no CPU fallback: if the library is missing, or no B200 is present,
+calls raise.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(_PKG, "liblwc_b200.so")
+
+SIM_IDENTITY, SIM_COSINE = 0, 1
+PREC_FP32, PREC_TF32X3, PREC_TF32, PREC_BF16 = 0, 1, 2, 3
+MEM_HOST, MEM_DEVICE = 0, 1
+MAX_CHOICES, MAX_VOTERS = 128, 128
+
+
+class LwcError(RuntimeError):
+    """Mirrors error::ResponseError { code, message } (src/error.rs:8-13)."""
+
+    def __init__(self, code, message):
+        super().__init__(f"[{code}] {message}")
+        self.code = code
+        self.message = message
+
+
+class BatchDesc(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in
+                ("R", "N", "D", "M", "similarity", "precision", "memory", "w_per_request")]
+
+
+class Config(ctypes.Structure):
+    _fields_ = [("device", ctypes.c_int32), ("chunk_requests", ctypes.c_int32), ("reserved", ctypes.c_uint64 * 4)]
+
+
+_lib = None
+
+
+def load_library():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: run `python __graft_entry__.py` (nvcc) first; "
+                          "there is no fallback implementation")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, i32, u64 = ctypes.c_void_p, ctypes.c_int32, ctypes.c_uint64
+    L.lwc_ctx_create.argtypes = [ctypes.POINTER(Config), ctypes.POINTER(vp)]
+    L.lwc_ctx_create.restype = i32
+    L.lwc_ctx_destroy.argtypes = [vp]
+    L.lwc_ctx_destroy.restype = None
+    L.lwc_last_error_message.argtypes = [vp]
+    L.lwc_last_error_message.restype = ctypes.c_char_p
+    L.lwc_version.restype = ctypes.c_char_p
+    for name in ("lwc_host_alloc", "lwc_device_alloc"):
+        getattr(L, name).argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(vp)]
+        getattr(L, name).restype = i32
+    for name in ("lwc_host_free", "lwc_device_free"):
+        getattr(L, name).argtypes = [vp, vp]
+        getattr(L, name).restype = i32
+    L.lwc_memcpy.argtypes = [vp, vp, vp, ctypes.c_size_t, i32]
+    L.lwc_memcpy.restype = i32
+    L.lwc_ctx_stream.argtypes = [vp]
+    L.lwc_ctx_stream.restype = vp
+    L.lwc_stream_synchronize.argtypes = [vp, vp]
+    L.lwc_stream_synchronize.restype = i32
+    L.lwc_score_batch.argtypes = [vp, ctypes.POINTER(BatchDesc)] + [vp] * 9
+    L.lwc_score_batch.restype = i32
+    L.lwc_kernel_for.argtypes = [vp, ctypes.POINTER(BatchDesc)]
+    L.lwc_kernel_for.restype = ctypes.c_char_p
+    L.lwc_launch_count.argtypes = [vp]
+    L.lwc_launch_count.restype = u64
+    L.lwc_merge_error_codes.argtypes = [ctypes.POINTER(ctypes.c_uint16), i32]
+    L.lwc_merge_error_codes.restype = i32
+    L.lwc_stage_f64.argtypes = [vp, vp, ctypes.c_size_t, vp]
+    L.lwc_stage_f64.restype = i32
+    _lib = L
+    return L
+
+
+def merge_error_codes(codes) -> int:
+    arr = (ctypes.c_uint16 * max(len(codes), 1))(*codes)
+    return load_library().lwc_merge_error_codes(arr, len(codes))
+
+
+def version() -> str:
+    return load_library().lwc_version().decode()
+
+
+def _np_ptr(a):
+    return ctypes.c_void_p(a.ctypes.data) if a is not None else None
+
+
+class HostBuffer:
+    """Pinned host memory from lwc_host_alloc, viewed as a numpy array."""
+
+    def __init__(self, ctx, shape, dtype):
+        self.ctx = ctx
+        self.shape = tuple(int(s) for s in shape)
+        self.dtype = np.dtype(dtype)
+        self.nbytes = int(np.prod(self.shape, dtype=np.int64)) * self.dtype.itemsize
+        p = ctypes.c_void_p()
+        ctx._check(ctx.lib.lwc_host_alloc(ctx.handle, self.nbytes, ctypes.byref(p)))
+        self.ptr = p.value
+        raw = (ctypes.c_char * max(self.nbytes, 1)).from_address(self.ptr)
+        self.array = np.frombuffer(raw, dtype=self.dtype, count=int(np.prod(self.shape, dtype=np.int64))).reshape(self.shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            self.ctx.lib.lwc_host_free(self.ctx.handle, ctypes.c_void_p(self.ptr))
+            self.ptr = None
+
+
+class DeviceBuffer:
+    """Device memory from lwc_device_alloc."""
+
+    def __init__(self, ctx, nbytes):
+        self.ctx = ctx
+        self.nbytes = int(nbytes)
+        p = ctypes.c_void_p()
+        ctx._check(ctx.lib.lwc_device_alloc(ctx.handle, self.nbytes, ctypes.byref(p)))
+        self.ptr = p.value
+
+    def upload(self, arr):
+        arr = np.ascontiguousarray(arr)
+        assert arr.nbytes <= self.nbytes
+        self.ctx._check(self.ctx.lib.lwc_memcpy(self.ctx.handle, ctypes.c_void_p(self.ptr), _np_ptr(arr), arr.nbytes, 0))
+        return self
+
+    def download(self, shape, dtype):
+        out = np.empty(shape, dtype)
+        assert out.nbytes <= self.nbytes
+        self.ctx._check(self.ctx.lib.lwc_memcpy(self.ctx.handle, _np_ptr(out), ctypes.c_void_p(self.ptr), out.nbytes, 1))
+        return out
+
+    def free(self):
+        if self.ptr:
+            self.ctx.lib.lwc_device_free(self.ctx.handle, ctypes.c_void_p(self.ptr))
+            self.ptr = None
+
+
+class Context:
+    def __init__(self, device=0, chunk_requests=0):
+        self.lib = load_library()
+        cfg = Config(device=device, chunk_requests=chunk_requests)
+        h = ctypes.c_void_p()
+        rc = self.lib.lwc_ctx_create(ctypes.byref(cfg), ctypes.byref(h))
+        if rc:
+            raise LwcError(rc, self.lib.lwc_last_error_message(None).decode())
+        self.handle = h
+
+    def close(self):
+        if self.handle:
+            self.lib.lwc_ctx_destroy(self.handle)
+            self.handle = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc):
+        if rc:
+            raise LwcError(rc, self.lib.lwc_last_error_message(self.handle).decode())
+
+    def stream(self) -> int:
+        return int(self.lib.lwc_ctx_stream(self.handle) or 0)
+
+    def launch_count(self) -> int:
+        return int(self.lib.lwc_launch_count(self.handle))
+
+    def kernel_for(self, R, N, D, M, similarity=SIM_COSINE, precision=PREC_FP32) -> str:
+        d = BatchDesc(R, N, D, M, similarity, precision, MEM_DEVICE, 1)
+        return self.lib.lwc_kernel_for(self.handle, ctypes.byref(d)).decode()
+
+    def synchronize(self, stream=None):
+        self._check(self.lib.lwc_stream_synchronize(self.handle, ctypes.c_void_p(stream) if stream else None))
+
+    def score_raw(self, desc, E, V, w, conf, cw, agree, winner, rank, stream=None):
+        """Pointers (ints / c_void_p / None) straight into lwc_score_batch."""
+        def vp(x):
+            return x if isinstance(x, ctypes.c_void_p) or x is None else ctypes.c_void_p(x)
+        self._check(self.lib.lwc_score_batch(self.handle, ctypes.byref(desc), vp(E), vp(V), vp(w), vp(conf), vp(cw),
+                                             vp(agree), vp(winner), vp(rank), vp(stream)))
+
+    def score_batch(self, E, V, w, similarity=SIM_COSINE, precision=PREC_FP32, outputs=("conf", "cw", "agree", "winner", "rank")):
+        """Host-memory call: numpy in, numpy out (lwc_score_batch with LWC_MEM_HOST)."""
+        V = np.ascontiguousarray(V, dtype=np.float32)
+        w = np.ascontiguousarray(w, dtype=np.float32)
+        R, M, N = V.shape
+        if similarity == SIM_COSINE:
+            E = np.ascontiguousarray(E, dtype=np.float32)
+            assert E.shape[:2] == (R, N), (E.shape, V.shape)
+            D = E.shape[2]
+        else:
+            E, D = None, 0
+        desc = BatchDesc(R, N, D, M, similarity, precision, MEM_HOST, 1 if w.ndim == 2 else 0)
+        out = {
+            "conf": np.full((R, N), np.nan, np.float32) if "conf" in outputs else None,
+            "cw": np.full((R, N), np.nan, np.float32) if "cw" in outputs else None,
+            "agree": np.full((R, M), -7.0, np.float32) if "agree" in outputs else None,
+            "winner": np.full((R,), -9, np.int32) if "winner" in outputs else None,
+            "rank": np.full((R, N), -9, np.int32) if "rank" in outputs else None,
+        }
+        self.score_raw(desc, _np_ptr(E), _np_ptr(V), _np_ptr(w), _np_ptr(out["conf"]), _np_ptr(out["cw"]),
+                       _np_ptr(out["agree"]), _np_ptr(out["winner"]), _np_ptr(out["rank"]))
+        return {k: v for k, v in out.items() if v is not None}
+
+    def score_batch_device(self, E, V, w, similarity=SIM_COSINE, precision=PREC_FP32):
+        """Device-resident call: uploads once, runs lwc_score_batch with LWC_MEM_DEVICE, downloads."""
+        V = np.ascontiguousarray(V, dtype=np.float32)
+        w = np.ascontiguousarray(w, dtype=np.float32)
+        R, M, N = V.shape
+        D = 0
+        bufs = []
+
+        def dev(arr_or_bytes):
+            b = DeviceBuffer(self, arr_or_bytes if isinstance(arr_or_bytes, int) else max(arr_or_bytes.nbytes, 4))
+            bufs.append(b)
+            if not isinstance(arr_or_bytes, int):
+                b.upload(arr_or_bytes)
+            return b
+
+        try:
+            dE = None
+            if similarity == SIM_COSINE:
+                E = np.ascontiguousarray(E, dtype=np.float32)
+                D = E.shape[2]
+                dE = dev(E)
+            dV, dw = dev(V), dev(w)
+            dconf, dcw = dev(4 * R * N + 4), dev(4 * R * N + 4)
+            dag, dwin, drk = dev(4 * R * M + 4), dev(4 * R + 4), dev(4 * R * N + 4)
+            desc = BatchDesc(R, N, D, M, similarity, precision, MEM_DEVICE, 1 if w.ndim == 2 else 0)
+            self.score_raw(desc, dE.ptr if dE else None, dV.ptr, dw.ptr, dconf.ptr, dcw.ptr, dag.ptr, dwin.ptr, drk.ptr)
+            self.synchronize()
+            return {"conf": dconf.download((R, N), np.float32), "cw": dcw.download((R, N), np.float32),
+                    "agree": dag.download((R, M), np.float32), "winner": dwin.download((R,), np.int32),
+                    "rank": drk.download((R, N), np.int32)}
+        finally:
+            for b in bufs:
+                b.free()
+
+    def stage_f64(self, src, dst):
+        src = np.ascontiguousarray(src, dtype=np.float64)
+        assert dst.dtype == np.float32 and dst.size >= src.size
+        self._check(self.lib.lwc_stage_f64(self.handle, _np_ptr(src), src.size, _np_ptr(dst)))

@@ -1,0 +1,289 @@
+"""Parity of the CUDA path (through the C ABI, liblwc_b200.so) against the CPU oracle.
+
+Bars (BASELINE.json north_star): winner index and rank order exact, confidences within 1e-5
+relative for the fp32-grade routes; the TF32 single-pass route has a stated wider tolerance
+(2e-3).  `parity_util` explains how "exact" is applied to near-ties that fp32 cannot resolve.
+Exact ties built from identical inputs must resolve to the lowest index on the device too.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from parity_util import CONF_ATOL, CONF_RTOL, check_rank, check_winner
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "tally_kats.json")))
+TF32_RTOL = 2e-3
+
+
+@pytest.fixture(scope="module")
+def lwc():
+    import lwc_b200
+
+    lwc_b200.load_library()  # raises if the CUDA library was not built: there is no fallback
+    return lwc_b200
+
+
+@pytest.fixture(scope="module")
+def ctx(lwc):
+    c = lwc.Context(device=0)
+    yield c
+    c.close()
+
+
+def compare(got, want, V, rtol=CONF_RTOL, atol=CONF_ATOL, gap=2e-6, min_agreement=1.0):
+    R = V.shape[0]
+    scale = np.maximum(np.abs(want["cw"]).max(axis=1, keepdims=True), 1e-30)
+    np.testing.assert_allclose(got["cw"] / scale, want["cw"] / scale, rtol=rtol, atol=max(rtol, 1e-6) * 0.1)
+    np.testing.assert_allclose(got["conf"], want["conf"], rtol=rtol, atol=atol)
+    absent = np.isnan(V[:, :, 0])
+    assert np.array_equal(np.isnan(got["agree"]), absent)
+    np.testing.assert_allclose(got["agree"][~absent], want["agree"][~absent], rtol=rtol, atol=atol)
+    agree = 0
+    for r in range(R):
+        agree += bool(check_winner(want["conf"][r], want["winner"][r], got["winner"][r], gap))
+        check_rank(want["conf"][r], want["rank"][r], got["rank"][r], gap)
+        if got["winner"][r] >= 0:
+            assert got["rank"][r][0] == got["winner"][r]
+    assert agree >= min_agreement * R, f"winner agreement {agree}/{R}"
+    return agree / max(R, 1)
+
+
+def case_arrays(case, n):
+    votes, weights = case["votes"], case["weights"]
+    M = len(votes)
+    V = np.zeros((1, M, n), np.float32)
+    w = np.zeros((1, M), np.float32)
+    for m in range(M):
+        V[0, m] = np.nan if votes[m] is None else [float(x) for x in votes[m]]
+        w[0, m] = np.nan if weights[m] is None else float(weights[m])
+    return V, w
+
+
+# ------------------------------------------------------------------ golden known answers
+
+@pytest.mark.parametrize("case", GOLDEN["tally"], ids=lambda c: c["name"])
+def test_identity_mode_reproduces_the_reference_tally(ctx, lwc, case):
+    """similarity = IDENTITY is client.rs:384-456 and nothing else."""
+    n = case["n_choices"]
+    V, w = case_arrays(case, n)
+    for fn in (ctx.score_batch, ctx.score_batch_device):
+        got = fn(None, V, w, similarity=lwc.SIM_IDENTITY)
+        want_cf = np.array([float(x) for x in case["confidence"]])
+        np.testing.assert_allclose(got["cw"][0], [float(x) for x in case["choice_weight"]], rtol=CONF_RTOL, atol=1e-9)
+        np.testing.assert_allclose(got["conf"][0], want_cf, rtol=CONF_RTOL, atol=CONF_ATOL)
+        check_winner(want_cf, case["winner"], got["winner"][0])
+        check_rank(want_cf, case["rank"], got["rank"][0])
+        for m, vc in enumerate(case["voter_confidence"]):
+            if vc is None:
+                assert np.isnan(got["agree"][0, m])
+            else:
+                assert got["agree"][0, m] == pytest.approx(float(vc), rel=CONF_RTOL, abs=CONF_ATOL)
+    if "error_codes" in case:
+        assert lwc.merge_error_codes(case["error_codes"]) == case["merged_status"]
+
+
+@pytest.mark.parametrize("case", GOLDEN["cosine"], ids=lambda c: c["name"])
+def test_cosine_golden(ctx, lwc, case):
+    E = np.array([[float(x) for x in row] for row in case["E"]], np.float32)[None]
+    n = E.shape[1]
+    V, w = case_arrays(case, n)
+    for fn in (ctx.score_batch, ctx.score_batch_device):
+        got = fn(E, V, w, similarity=lwc.SIM_COSINE)
+        np.testing.assert_allclose(got["cw"][0], case["choice_weight"], rtol=CONF_RTOL, atol=1e-6)
+        np.testing.assert_allclose(got["conf"][0], case["confidence"], rtol=CONF_RTOL, atol=CONF_ATOL)
+        assert got["winner"][0] == case["winner"]
+        assert list(got["rank"][0]) == case["rank"]
+
+
+def test_exact_tie_resolves_to_lowest_index(ctx, lwc):
+    """K10 on the device, in both modes: identical rows + symmetric votes give bit-equal
+    confidences, and the lowest index must win."""
+    for N, D in ((4, 64), (16, 1536), (32, 3072), (48, 100), (128, 64)):
+        rng = np.random.default_rng(N)
+        E = rng.standard_normal((3, N, D)).astype(np.float32)
+        E[:, 2] = E[:, 0]
+        V = np.zeros((3, 2, N), np.float32)
+        V[:, 0, 0] = 1
+        V[:, 1, 2] = 1
+        w = np.full((3, 2), 1.25, np.float32)
+        for sim in (lwc.SIM_COSINE, lwc.SIM_IDENTITY):
+            got = ctx.score_batch(E, V, w, similarity=sim)
+            assert np.all(got["conf"][:, 0] == got["conf"][:, 2])
+            assert np.all(got["winner"] == 0)
+            assert np.all(got["rank"][:, 0] == 0) and np.all(got["rank"][:, 1] == 2)
+
+
+# ------------------------------------------------------------------ seeded random parity
+
+SHAPES = [
+    # (R, N, D, M)            route
+    (37, 16, 1536, 4),      # small16: the cfg2 shape
+    (19, 32, 3072, 4),      # small32: the cfg3 shape
+    (23, 2, 16, 1),         # minimum pool
+    (11, 7, 36, 3),         # ragged N, D % 16 != 0
+    (9, 16, 20, 128),       # maximum voters
+    (13, 17, 1000, 5),      # small32 with padding rows
+    (5, 31, 4, 2),          # D smaller than one chunk
+    (7, 12, 50, 4),         # D % 4 != 0 -> generic
+    (6, 33, 128, 6),        # generic64
+    (4, 64, 257, 9),        # generic64, odd D
+    (3, 100, 96, 16),       # generic128
+    (3, 128, 512, 16),      # generic128: the cfg4 pool size
+    (8, 20, 64, 0),         # no voters at all
+]
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+@pytest.mark.parametrize("memory", ["host", "device"])
+def test_random_parity_cosine(ctx, lwc, oracle, shape, memory):
+    from lwc_b200 import synth
+
+    R, N, D, M = shape
+    E, V, w, _ = synth.make_batch(R, N, D, M, seed=1000 + N * 7 + D, edge_cases=False)
+    if M:
+        w[0, 0] = np.nan  # weight None -> 0
+        if R > 2:
+            V[2] = np.nan  # every voter absent
+    fn = ctx.score_batch if memory == "host" else ctx.score_batch_device
+    got = fn(E, V, w, similarity=lwc.SIM_COSINE)
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    compare(got, want, V)
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+def test_random_parity_identity(ctx, lwc, oracle, shape):
+    from lwc_b200 import synth
+
+    R, N, D, M = shape
+    _, V, w, _ = synth.make_batch(R, N, 4, M, seed=77 + N, edge_cases=False)
+    got = ctx.score_batch(None, V, w, similarity=lwc.SIM_IDENTITY)
+    want = oracle.score_f64(np.zeros((R, N, 0), np.float32), V, w, oracle.SIM_IDENTITY)
+    compare(got, want, V)
+    # and against the Decimal-typed port of the reference block
+    port = oracle.score_port(np.zeros((R, N, 0), np.float32), V, w, oracle.SIM_IDENTITY)
+    np.testing.assert_allclose(got["conf"], port["conf"], rtol=CONF_RTOL, atol=CONF_ATOL)
+
+
+@pytest.mark.parametrize("shape", [(16, 16, 1536, 4), (8, 32, 3072, 4), (5, 9, 40, 3)],
+                         ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+def test_tf32_single_pass_has_the_stated_wider_tolerance(ctx, lwc, oracle, shape):
+    from lwc_b200 import synth
+
+    R, N, D, M = shape
+    E, V, w, _ = synth.make_batch(R, N, D, M, seed=4242, edge_cases=False)
+    got = ctx.score_batch(E, V, w, similarity=lwc.SIM_COSINE, precision=lwc.PREC_TF32)
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    compare(got, want, V, rtol=TF32_RTOL, atol=1e-5, gap=5e-3, min_agreement=0.95)
+
+
+def test_unit_embeddings_with_orthonormal_rows_bridge_to_the_tally(ctx, lwc, oracle):
+    """K6 at scale: orthonormal candidates make S = I, so cosine mode must equal identity mode."""
+    rng = np.random.default_rng(9)
+    R, N, D, M = 12, 16, 64, 5
+    q, _ = np.linalg.qr(rng.standard_normal((R, D, D)))
+    E = (q[:, :N, :] * rng.uniform(0.5, 3.0, (R, N, 1))).astype(np.float32)
+    V = rng.random((R, M, N)).astype(np.float32)
+    V /= V.sum(axis=2, keepdims=True)
+    w = rng.uniform(0.5, 2, (R, M)).astype(np.float32)
+    a = ctx.score_batch(E, V, w, similarity=lwc.SIM_COSINE)
+    b = ctx.score_batch(None, V, w, similarity=lwc.SIM_IDENTITY)
+    np.testing.assert_allclose(a["conf"], b["conf"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(a["cw"], b["cw"], rtol=1e-5, atol=1e-6)
+
+
+# ------------------------------------------------------------------ BASELINE.json shapes
+
+def properties_hold(got, V):
+    conf, rank, winner = got["conf"], got["rank"], got["winner"]
+    R, N = conf.shape
+    s = conf.sum(axis=1)
+    scored = winner >= 0
+    np.testing.assert_allclose(s[scored], 1.0, rtol=0, atol=2e-6)
+    assert np.all(s[~scored] == 0)
+    assert np.all(np.sort(rank, axis=1) == np.arange(N)[None, :])  # permutation
+    sorted_conf = np.take_along_axis(conf, rank, axis=1)
+    assert np.all(sorted_conf[:, :-1] >= sorted_conf[:, 1:])      # descending, on the device's own values
+    ties = sorted_conf[:, :-1] == sorted_conf[:, 1:]
+    assert np.all(rank[:, :-1][ties] < rank[:, 1:][ties])          # stable
+    assert np.all(rank[scored, 0] == winner[scored])
+    absent = np.isnan(V[:, :, 0])
+    assert np.array_equal(np.isnan(got["agree"]), absent)
+
+
+def test_cfg2_full_size(ctx, lwc, oracle):
+    """BASELINE config 2: 4,096 requests x 16 candidates x 1536 dims, 4 voters, incl. the 1 %
+    injected edge cases.  Oracle on a 512-request slice; properties on everything."""
+    from lwc_b200 import synth
+
+    R, N, D, M = synth.CONFIGS["cfg2"]
+    E, V, w, kinds = synth.make_batch(R, N, D, M)
+    assert ctx.kernel_for(R, N, D, M) == "small16_tf32x3"
+    got = ctx.score_batch(E, V, w)
+    properties_hold(got, V)
+    sl = np.r_[0:384, np.array(sorted(sum(kinds.values(), [])), int)]
+    want = oracle.score_f64(E[sl], V[sl], w[sl], oracle.SIM_COSINE)
+    sub = {k: v[sl] for k, v in got.items()}
+    assert compare(sub, want, V[sl]) == 1.0
+    for r in kinds["all_absent"]:
+        assert got["winner"][r] == -1 and np.all(got["conf"][r] == 0)
+    for r in kinds["tie"]:
+        assert got["conf"][r, 0] == got["conf"][r, 1] and got["winner"][r] == 0
+    for r in kinds["duplicate"]:
+        assert got["conf"][r, 0] == got["conf"][r, 1]
+    # request order and host chunking must not change a single bit
+    perm = np.random.default_rng(1).permutation(R)[:600]
+    again = ctx.score_batch_device(E[perm], V[perm], w[perm])
+    for k in got:
+        assert np.array_equal(again[k], got[k][perm], equal_nan=True), k
+
+
+def test_cfg3_shape_slice(ctx, lwc, oracle):
+    from lwc_b200 import synth
+
+    _, N, D, M = synth.CONFIGS["cfg3"]
+    R = 300
+    E, V, w, kinds = synth.make_batch(R, N, D, M, seed=3)
+    assert ctx.kernel_for(R, N, D, M) == "small32_tf32x3"
+    got = ctx.score_batch(E, V, w)
+    properties_hold(got, V)
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    assert compare(got, want, V) == 1.0
+
+
+def test_cfg4_shape_slice(ctx, lwc, oracle):
+    from lwc_b200 import synth
+
+    _, N, D, M = synth.CONFIGS["cfg4"]
+    R = 24
+    E, V, w, kinds = synth.make_batch(R, N, D, M, seed=4)
+    got = ctx.score_batch(E, V, w)
+    properties_hold(got, V)
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    assert compare(got, want, V) == 1.0
+
+
+# ------------------------------------------------------------------ argument errors
+
+def test_argument_errors_map_to_400(ctx, lwc):
+    V = np.zeros((1, 1, 200), np.float32)
+    w = np.ones((1, 1), np.float32)
+    with pytest.raises(lwc.LwcError) as ei:
+        ctx.score_batch(None, V, w, similarity=lwc.SIM_IDENTITY)  # N > LWC_MAX_CHOICES
+    assert ei.value.code == 400
+    with pytest.raises(lwc.LwcError) as ei:
+        ctx.score_batch(np.zeros((1, 4, 8), np.float32), np.zeros((1, 1, 4), np.float32), w, similarity=7)
+    assert ei.value.code == 400
+    # R = 0 is a valid empty batch
+    out = ctx.score_batch(np.zeros((0, 4, 8), np.float32), np.zeros((0, 2, 4), np.float32), np.zeros((0, 2), np.float32))
+    assert out["conf"].shape == (0, 4)
+
+
+def test_stage_f64(ctx, lwc):
+    src = np.random.default_rng(0).standard_normal(1000)
+    dst = np.empty(1000, np.float32)
+    ctx.stage_f64(src, dst)
+    assert np.array_equal(dst, src.astype(np.float32))
