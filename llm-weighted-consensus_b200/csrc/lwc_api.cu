@@ -3,6 +3,7 @@
 // host-memory pipeline (H2D on a copy stream overlapped with kernels on the compute stream).
 // There is no CPU fallback anywhere in this file: without a CUDA device every entry point
 // that computes returns 503/500.
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <cmath>
@@ -16,6 +17,7 @@
 #include "../../include/lwc_b200.h"
 #include "score_generic.cuh"
 #include "score_small.cuh"
+#include "score_stream.cuh"
 
 #define LWC_VERSION_STRING "lwc_b200 0.1.0 (sm_100a)"
 
@@ -46,6 +48,12 @@ struct lwc_ctx {
     Slot slots[2];
     int small_kw = 4; // warps per request in the small-pool kernel (LWC_SMALL_KW)
     int small_u = 0;  // k-chunks in flight per lane, 0 = per-shape default (LWC_SMALL_U)
+    int small_impl = 0;   // 0 = persistent streaming kernel, 1 = one-CTA-per-request kernel (LWC_SMALL_IMPL=direct)
+    int stream_ncw = 0;   // consumer warps of the streaming kernel, 0 = per-shape default (LWC_STREAM_NCW)
+    int stream_kc = 0;    // upper bound on columns per stage, 0 = as large as fits (LWC_STREAM_KC)
+    int stream_slots = 0; // ring depth override (LWC_STREAM_SLOTS)
+    int stream_nf = 0;    // finaliser warps, 0 = 1 (LWC_STREAM_NF)
+    int max_smem_optin = 0;
 };
 
 namespace {
@@ -157,10 +165,95 @@ cudaError_t launch_small(const lwc::ScoreParams &p, cudaStream_t st, int kw, int
     }
 }
 
+// cuTensorMapEncodeTiled is a driver entry point; fetch it through the runtime so that the
+// library does not link libcuda directly.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void *sym = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    }
+    return fn;
+}
+
+// E viewed as a rank-3 fp32 tensor [R][N][D]; one box = [1][rows][cols] (dense in shared memory).
+[[maybe_unused]] bool make_tensor_map_e(CUtensorMap *tm, const float *E, int R, int N, int D, int box_rows, int box_cols) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) return false;
+    cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)N, (cuuint64_t)R};
+    cuuint64_t strides[2] = {(cuuint64_t)D * 4, (cuuint64_t)N * D * 4};
+    cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    return fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float *>(E), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int NT, bool X3, int NCW, int NF>
+cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
+    using C = lwc::StreamCfg<NT, X3, NCW, NF>;
+    const size_t avail = (size_t)ctx->max_smem_optin - 128 - C::fixed_bytes();
+    lwc::StreamGeom geo;
+    // stage width: 3 KB per row copy is where the bulk-copy engine reaches HBM speed
+    // (profiles/r1_tma_probe.txt); shrink it until at least 3 stages fit.
+    const int dpad = (p.D + 15) / 16 * 16;
+    int ks = ctx->stream_kc >= 16 ? ctx->stream_kc : 768;
+    if (ks > dpad) ks = dpad;
+    while (ks > 64 && avail / C::stage_bytes(ks) < 3) ks = ((ks / 2) + 15) / 16 * 16;
+    geo.ks = ks;
+    geo.stages = (int)(avail / C::stage_bytes(ks));
+    if (geo.stages > C::MAXS) geo.stages = C::MAXS;
+    if (ctx->stream_slots >= 1 && ctx->stream_slots < geo.stages) geo.stages = ctx->stream_slots;
+    if (geo.stages < 1) return cudaErrorInvalidConfiguration;
+    static bool configured[64] = {false};
+    if (!configured[ctx->device & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_stream_kernel<NT, X3, NCW, NF>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
+        if (e != cudaSuccess) return e;
+        configured[ctx->device & 63] = true;
+    }
+    const int grid = p.R < ctx->sm_count ? p.R : ctx->sm_count;
+    lwc::score_stream_kernel<NT, X3, NCW, NF><<<grid, C::THREADS, C::smem_bytes(geo.ks, geo.stages), st>>>(p, geo);
+    return cudaGetLastError();
+}
+
+template <int NT, bool X3>
+cudaError_t launch_stream(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
+    const int ncw = ctx->stream_ncw ? ctx->stream_ncw : (NT == 16 ? 12 : 8);
+    const int nf = ctx->stream_nf ? ctx->stream_nf : (NT == 16 ? 4 : 2);
+    switch (ncw * 10 + nf) {
+        case 41: return launch_stream_one<NT, X3, 4, 1>(ctx, p, st);
+        case 42: return launch_stream_one<NT, X3, 4, 2>(ctx, p, st);
+        case 44: return launch_stream_one<NT, X3, 4, 4>(ctx, p, st);
+        case 81: return launch_stream_one<NT, X3, 8, 1>(ctx, p, st);
+        case 82: return launch_stream_one<NT, X3, 8, 2>(ctx, p, st);
+        case 83: return launch_stream_one<NT, X3, 8, 3>(ctx, p, st);
+        case 84: return launch_stream_one<NT, X3, 8, 4>(ctx, p, st);
+        case 86: return launch_stream_one<NT, X3, 8, 6>(ctx, p, st);
+        case 122: return launch_stream_one<NT, X3, 12, 2>(ctx, p, st);
+        case 124: return launch_stream_one<NT, X3, 12, 4>(ctx, p, st);
+        default: return launch_stream_one<NT, X3, 8, 2>(ctx, p, st);
+    }
+}
+
 int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStream_t st) {
     if (p.R == 0) return LWC_OK;
     cudaError_t e = cudaSuccess;
-    if (pl.route == ROUTE_SMALL) {
+    if (pl.route == ROUTE_SMALL && ctx->small_impl == 0) {
+        if (pl.np == 16)
+            e = pl.x3 ? launch_stream<16, true>(ctx, p, st) : launch_stream<16, false>(ctx, p, st);
+        else
+            e = pl.x3 ? launch_stream<32, true>(ctx, p, st) : launch_stream<32, false>(ctx, p, st);
+    } else if (pl.route == ROUTE_SMALL) {
         if (pl.np == 16)
             e = pl.x3 ? launch_small<16, true>(p, st, ctx->small_kw, ctx->small_u)
                       : launch_small<16, false>(p, st, ctx->small_kw, ctx->small_u);
@@ -315,6 +408,14 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     ctx->chunk_requests = cfg ? cfg->chunk_requests : 0;
     if (const char *s = getenv("LWC_SMALL_KW")) ctx->small_kw = atoi(s);
     if (const char *s = getenv("LWC_SMALL_U")) ctx->small_u = atoi(s);
+    if (const char *s = getenv("LWC_SMALL_IMPL")) ctx->small_impl = (strcmp(s, "direct") == 0) ? 1 : 0;
+    if (const char *s = getenv("LWC_STREAM_NCW")) ctx->stream_ncw = atoi(s);
+    if (const char *s = getenv("LWC_STREAM_KC")) ctx->stream_kc = atoi(s);
+    if (const char *s = getenv("LWC_STREAM_SLOTS")) ctx->stream_slots = atoi(s);
+    if (const char *s = getenv("LWC_STREAM_NF")) ctx->stream_nf = atoi(s);
+    if (ctx->stream_ncw != 0 && ctx->stream_ncw != 4 && ctx->stream_ncw != 8 && ctx->stream_ncw != 12) ctx->stream_ncw = 0;
+    if (ctx->stream_kc < 0 || ctx->stream_kc % 16) ctx->stream_kc = 0;
+    cudaDeviceGetAttribute(&ctx->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     if (ctx->small_kw != 2 && ctx->small_kw != 4 && ctx->small_kw != 8) ctx->small_kw = 4;
     if (ctx->small_u != 0 && ctx->small_u != 2 && ctx->small_u != 4) ctx->small_u = 0;
     bool ok = cudaSetDevice(dev) == cudaSuccess &&

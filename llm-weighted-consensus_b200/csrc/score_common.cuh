@@ -58,18 +58,31 @@ __device__ __forceinline__ float4 ld_stream_f4(const float *p) {
     return r;
 }
 
-// Warp-wide tail of the path for one request whose candidates fit one warp (N <= 32):
-// lane j owns choice j.  S is the raw Gram matrix E E^T in shared memory (pitch `pitch`),
-// ignored when !p.cosine.
-__device__ __forceinline__ void warp_tally_and_rank(const ScoreParams &p, int r, const float *S, int pitch,
-                                                    int lane) {
+// Warp-wide tail of the path for one request whose candidates fit one warp (N <= NTP <= 32):
+// lane j owns choice j.  S is the raw Gram matrix E E^T in shared memory (pitch `pitch`, rows
+// and columns >= N all zero), ignored when !p.cosine.  The first MU voters' rows/weights may
+// arrive prefetched in registers (pv[m] = V[r][m][lane], pw[m] = w[m]); the rest are read from
+// global memory.  Loops run to the compile-time pool size NTP so that their shuffles, shared
+// loads and FMAs pipeline; padding lanes carry zeros.
+template <int MU, int NTP>
+__device__ __forceinline__ void warp_tally_and_rank_pf(const ScoreParams &p, int r, const float *S, int pitch,
+                                                       int lane, const float *pv, const float *pw) {
     const int N = p.N, M = p.M;
     const float *Vr = p.V + (size_t)r * M * N;
     const float *wr = p.w + (p.w_per_request ? (size_t)r * M : 0);
     const bool act = lane < N;
 
     float t = 0.f;
-    for (int m = 0; m < M; ++m) {
+#pragma unroll
+    for (int m = 0; m < MU; ++m) {
+        if (m < M) {
+            const float v0 = __shfl_sync(kFullMask, pv[m], 0);
+            float wm = pw[m];
+            if (isnan(wm)) wm = 0.f;
+            if (!isnan(v0) && act) t = fmaf(pv[m], wm, t);
+        }
+    }
+    for (int m = MU; m < M; ++m) {
         const float v0 = __ldg(Vr + (size_t)m * N);
         if (isnan(v0)) continue; // voter without a vote (client.rs:410) -- warp-uniform
         float wm = __ldg(wr + m);
@@ -79,14 +92,16 @@ __device__ __forceinline__ void warp_tally_and_rank(const ScoreParams &p, int r,
 
     float c = t;
     if (p.cosine) {
-        const float d = act ? S[lane * pitch + lane] : 0.f;
+        const int jl = lane < NTP ? lane : 0;
+        const float d = act ? S[jl * pitch + jl] : 0.f;
         const float rn = d > 0.f ? 1.0f / sqrtf(d) : 0.f; // zero-norm row: E^_i = 0
-        const float u = t * rn;
+        const float u = t * rn;                            // 0 on padding lanes
+        float col[NTP];
+#pragma unroll
+        for (int i = 0; i < NTP; ++i) col[i] = S[i * pitch + jl];
         float acc = 0.f;
-        for (int i = 0; i < N; ++i) {
-            const float ui = __shfl_sync(kFullMask, u, i);
-            if (act) acc = fmaf(ui, S[i * pitch + lane], acc);
-        }
+#pragma unroll
+        for (int i = 0; i < NTP; ++i) acc = fmaf(__shfl_sync(kFullMask, u, i), col[i], acc);
         c = acc * rn;
     }
     if (!act) c = 0.f;
@@ -106,14 +121,30 @@ __device__ __forceinline__ void warp_tally_and_rank(const ScoreParams &p, int r,
     }
     if (p.rank) {
         int pos = 0;
-        for (int i = 0; i < N; ++i) {
+#pragma unroll
+        for (int i = 0; i < NTP; ++i) {
             const float ci = __shfl_sync(kFullMask, cf, i);
-            pos += (ci > cf || (ci == cf && i < lane)) ? 1 : 0;
+            pos += (i < N && (ci > cf || (ci == cf && i < lane))) ? 1 : 0;
         }
         if (act) p.rank[(size_t)r * N + pos] = lane;
     }
     if (p.agree) {
-        for (int m = 0; m < M; ++m) {
+        float part[MU > 0 ? MU : 1];
+#pragma unroll
+        for (int m = 0; m < MU; ++m) part[m] = (act && m < M) ? cf * pv[m] : 0.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int m = 0; m < MU; ++m) part[m] += __shfl_xor_sync(kFullMask, part[m], o);
+        }
+#pragma unroll
+        for (int m = 0; m < MU; ++m) {
+            if (m < M) {
+                const float v0 = __shfl_sync(kFullMask, pv[m], 0);
+                if (lane == 0) p.agree[(size_t)r * M + m] = isnan(v0) ? __int_as_float(0x7fc00000) : part[m];
+            }
+        }
+        for (int m = MU; m < M; ++m) {
             const float v0 = __ldg(Vr + (size_t)m * N);
             float a;
             if (isnan(v0)) {
@@ -124,6 +155,12 @@ __device__ __forceinline__ void warp_tally_and_rank(const ScoreParams &p, int r,
             if (lane == 0) p.agree[(size_t)r * M + m] = a;
         }
     }
+}
+
+template <int NTP>
+__device__ __forceinline__ void warp_tally_and_rank(const ScoreParams &p, int r, const float *S, int pitch,
+                                                    int lane) {
+    warp_tally_and_rank_pf<0, NTP>(p, r, S, pitch, lane, nullptr, nullptr);
 }
 
 } // namespace lwc

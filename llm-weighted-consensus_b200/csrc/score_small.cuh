@@ -19,18 +19,19 @@
 
 namespace lwc {
 
-__device__ __forceinline__ uint32_t to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return r;
-}
-
 __device__ __forceinline__ void mma_m16n8k8_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                                  uint32_t b0, uint32_t b1) {
     asm volatile(
         "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
         : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// hi = x rounded to TF32 (nearest, ties away), lo = the exact remainder x - hi.  The tensor core
+// reads only the top 19 bits of an operand, so lo needs no further rounding instruction.
+__device__ __forceinline__ void split_tf32(float x, uint32_t &hi, uint32_t &lo) {
+    hi = (__float_as_uint(x) + 0x1000u) & 0xffffe000u;
+    lo = __float_as_uint(x - __uint_as_float(hi));
 }
 
 // NT: padded pool size (16 or 32).  X3: error-compensated 3xTF32 (true) or single TF32 (false).
@@ -108,11 +109,12 @@ score_small_kernel(const ScoreParams p) {
                     for (int q = 0; q < RPL; ++q) {
                         const float x = h ? buf[u][q].z : buf[u][q].x;
                         const float y = h ? buf[u][q].w : buf[u][q].y;
-                        xh[q] = to_tf32(x);
-                        yh[q] = to_tf32(y);
                         if (X3) {
-                            xl[q] = to_tf32(x - __uint_as_float(xh[q]));
-                            yl[q] = to_tf32(y - __uint_as_float(yh[q]));
+                            split_tf32(x, xh[q], xl[q]);
+                            split_tf32(y, yh[q], yl[q]);
+                        } else {
+                            xh[q] = __float_as_uint(x) + 0x1000u; // RNA; the low 13 bits are ignored
+                            yh[q] = __float_as_uint(y) + 0x1000u;
                         }
                     }
 #pragma unroll
@@ -205,7 +207,7 @@ score_small_kernel(const ScoreParams p) {
         return;
     }
 
-    warp_tally_and_rank(p, r, tile, PITCH, lane);
+    warp_tally_and_rank<NT>(p, r, tile, PITCH, lane);
 }
 
 } // namespace lwc
