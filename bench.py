@@ -117,7 +117,7 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.samples)}
 
 
-def cpu_baseline(E, V, w, budget_s=12.0):
+def cpu_baseline(E, V, w, budget_s=10.0):
     """Reference-typed CPU port on all host cores, bounded sample of the same workload."""
     import oracle
 
@@ -128,7 +128,7 @@ def cpu_baseline(E, V, w, budget_s=12.0):
     per_req = max(t / probe, 1e-9)
     n = int(min(R, max(probe, budget_s / per_req)))
     reps, total_req, total_s = 0, 0, 0.0
-    while total_s < budget_s and reps < 64:
+    while total_s < budget_s and reps < 4096:
         total_s += oracle.score_port(E[:n], V[:n], w[:n], oracle.SIM_COSINE)["seconds"]
         total_req += n
         reps += 1
@@ -189,6 +189,8 @@ def run_b200(args):
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
+    if args.workload != WORKLOAD:
+        return run_other_workload(args, torch, lwc_b200, synth, local_rank)
     R, N, D, M = synth.CONFIGS[WORKLOAD]
     ctx = lwc_b200.Context(device=local_rank)
     kernel = ctx.kernel_for(R, N, D, M)
@@ -323,6 +325,62 @@ def run_b200(args):
     return 0
 
 
+def run_other_workload(args, torch, lwc_b200, synth, local_rank):
+    """Kernel-only measurement of another BASELINE.json shape (cfg3/cfg4), single GPU, inputs generated in
+    HBM.  Not the driver's bench line: it feeds profiles/ and DESIGN.md."""
+    R, N, D, M = synth.CONFIGS[args.workload]
+    if args.requests:
+        R = args.requests
+    prec = {"fp32": lwc_b200.PREC_FP32, "tf32": lwc_b200.PREC_TF32}[args.precision]
+    ctx = lwc_b200.Context(device=local_rank)
+    kernel = ctx.kernel_for(R, N, D, M, precision=prec)
+    g = torch.Generator(device="cuda").manual_seed(7)
+    n_rot = 2
+    dE = []
+    for _ in range(n_rot):
+        e = torch.randn((R, N, D), dtype=torch.float32, device="cuda", generator=g)
+        e *= torch.exp(0.5 * torch.randn((R, N, 1), dtype=torch.float32, device="cuda", generator=g))
+        dE.append(e)
+    V = synth.votes(R, N, M, seed=11)
+    w = synth.weights(R, M, seed=11)
+    dV, dw = torch.from_numpy(V).cuda(), torch.from_numpy(w).cuda()
+    outs = [torch.empty((R, N), dtype=torch.float32, device="cuda"), torch.empty((R, N), dtype=torch.float32, device="cuda"),
+            torch.empty((R, M), dtype=torch.float32, device="cuda"), torch.empty((R,), dtype=torch.int32, device="cuda"),
+            torch.empty((R, N), dtype=torch.int32, device="cuda")]
+    desc = lwc_b200.BatchDesc(R, N, D, M, lwc_b200.SIM_COSINE, prec, lwc_b200.MEM_DEVICE, 1)
+    stream = torch.cuda.Stream()
+
+    def step(i):
+        ctx.score_raw(desc, dE[i % n_rot].data_ptr(), dV.data_ptr(), dw.data_ptr(), *[o.data_ptr() for o in outs],
+                      stream=stream.cuda_stream)
+
+    for i in range(args.warmup):
+        step(i)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+        for i in range(args.steps):
+            step(i)
+        ev1.record(stream)
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1) / args.steps
+    peak, peak_src = load_peaks()
+    nbytes = R * synth.algorithmic_bytes_per_request(N, D, M)
+    flops = R * synth.algorithmic_flops_per_request(N, D, M)
+    achieved = nbytes / (ms * 1e-3) / 1e9
+    print(json.dumps({
+        "metric": METRIC, "value": R / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms, "dtype": "f32", "data": "synthetic (generated in HBM)",
+        "config": {"workload": f"{args.workload}: {R} requests x {N} candidates x {D}-dim fp32, {M} voters",
+                   "kernel": kernel, "precision": args.precision, "l2": f"{n_rot} rotating batches of {dE[0].numel() * 4 / 1e9:.2f} GB"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "peak_source": peak_src, "bytes_per_launch": nbytes, "algorithmic_tflops": flops / (ms * 1e-3) / 1e12},
+        "gpu_launches": args.steps}), flush=True)
+    ctx.close()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -330,6 +388,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default=WORKLOAD, choices=["cfg2", "cfg3", "cfg4"],
+                    help="cfg2 is the bench line; cfg3/cfg4 are kernel-only side measurements")
+    ap.add_argument("--requests", type=int, default=0, help="override R for --workload cfg3/cfg4")
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

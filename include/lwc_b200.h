@@ -21,6 +21,9 @@
  *   lwc_stage_f64 .......... the Vec<f64> -> device fp32 hop for
  *                            embeddings::response::Embedding.embedding
  *                            (src/embeddings/response.rs:19-24).
+ *   lwc_vote_from_logprobs . the numeric tail of get_vote, client.rs:1765-1791: exp(logprob) of
+ *                            the sibling-leaf alternatives, accumulated per choice, divided by
+ *                            the probability sum.
  *
  * Error convention mirrors error::ResponseError { code: u16, .. } (src/error.rs:8-13):
  * every function returns 0 on success or an HTTP-style status -- 400 for a malformed
@@ -141,6 +144,16 @@ int32_t lwc_merge_error_codes(const uint16_t *codes, int32_t n_voters);
 /* replaces: the f64 -> fp32 hop for Embedding.embedding (embeddings/response.rs:21).
  * Converts n doubles at src (host) to floats at dst (host, typically from lwc_host_alloc). */
 int32_t lwc_stage_f64(lwc_ctx *ctx, const double *src, size_t n, float *dst);
+
+/* replaces: client.rs:1765-1791 (the producer of Delta.vote, response.rs:189), batched.
+ *   logprob [n_rows][n_top] fp32  TopLogprob.logprob of each alternative (NaN = logprob None)
+ *   leaf    [n_rows][n_top] i32   choice index the alternative's character selects in the lowest
+ *                                 prefix-tree branch, or -1 when it is not a sibling leaf
+ *   V       [n_rows][n_choices]   vote rows out; a row whose probability sum is 0 (unreachable!() in
+ *                                 the reference) is written as NaN = "voter without a vote"
+ * `memory` as in lwc_batch_desc; device calls are asynchronous on `stream`. */
+int32_t lwc_vote_from_logprobs(lwc_ctx *ctx, int32_t n_rows, int32_t n_top, int32_t n_choices, const float *logprob,
+                               const int32_t *leaf, float *V, int32_t memory, void *stream);
 
 #ifdef __cplusplus
 }

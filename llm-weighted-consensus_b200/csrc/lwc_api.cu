@@ -18,6 +18,7 @@
 #include "score_generic.cuh"
 #include "score_small.cuh"
 #include "score_stream.cuh"
+#include "vote_kernel.cuh"
 
 #define LWC_VERSION_STRING "lwc_b200 0.1.0 (sm_100a)"
 
@@ -49,6 +50,7 @@ struct lwc_ctx {
     int small_kw = 4; // warps per request in the small-pool kernel (LWC_SMALL_KW)
     int small_u = 0;  // k-chunks in flight per lane, 0 = per-shape default (LWC_SMALL_U)
     int small_impl = 0;   // 0 = persistent streaming kernel, 1 = one-CTA-per-request kernel (LWC_SMALL_IMPL=direct)
+    int force_stream = 0; // LWC_SMALL_IMPL=stream: streaming kernel for every small shape
     int stream_ncw = 0;   // consumer warps of the streaming kernel, 0 = per-shape default (LWC_STREAM_NCW)
     int stream_kc = 0;    // upper bound on columns per stage, 0 = as large as fits (LWC_STREAM_KC)
     int stream_slots = 0; // ring depth override (LWC_STREAM_SLOTS)
@@ -248,7 +250,10 @@ cudaError_t launch_stream(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t 
 int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStream_t st) {
     if (p.R == 0) return LWC_OK;
     cudaError_t e = cudaSuccess;
-    if (pl.route == ROUTE_SMALL && ctx->small_impl == 0) {
+    // 32-candidate pools with the compensated 3xTF32 Gram are bound by the legacy mma.sync pipe, not by
+    // HBM; there the one-CTA-per-request kernel (more warps in flight) measured 83 % vs 80 % of HBM peak.
+    const bool stream_route = ctx->small_impl == 0 && !(pl.np == 32 && pl.x3 && !ctx->force_stream);
+    if (pl.route == ROUTE_SMALL && stream_route) {
         if (pl.np == 16)
             e = pl.x3 ? launch_stream<16, true>(ctx, p, st) : launch_stream<16, false>(ctx, p, st);
         else
@@ -408,7 +413,10 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     ctx->chunk_requests = cfg ? cfg->chunk_requests : 0;
     if (const char *s = getenv("LWC_SMALL_KW")) ctx->small_kw = atoi(s);
     if (const char *s = getenv("LWC_SMALL_U")) ctx->small_u = atoi(s);
-    if (const char *s = getenv("LWC_SMALL_IMPL")) ctx->small_impl = (strcmp(s, "direct") == 0) ? 1 : 0;
+    if (const char *s = getenv("LWC_SMALL_IMPL")) {
+        ctx->small_impl = (strcmp(s, "direct") == 0) ? 1 : 0;
+        ctx->force_stream = (strcmp(s, "stream") == 0) ? 1 : 0;
+    }
     if (const char *s = getenv("LWC_STREAM_NCW")) ctx->stream_ncw = atoi(s);
     if (const char *s = getenv("LWC_STREAM_KC")) ctx->stream_kc = atoi(s);
     if (const char *s = getenv("LWC_STREAM_SLOTS")) ctx->stream_slots = atoi(s);
@@ -553,6 +561,49 @@ int32_t lwc_merge_error_codes(const uint16_t *codes, int32_t n_voters) {
         }
     }
     return have ? merged : 500; // AllVotesFailed(None) -> 500 (score/completions/error.rs:41)
+}
+
+int32_t lwc_vote_from_logprobs(lwc_ctx *ctx, int32_t n_rows, int32_t n_top, int32_t n_choices, const float *logprob,
+                               const int32_t *leaf, float *V, int32_t memory, void *stream) {
+    if (!ctx) return LWC_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (n_rows < 0 || n_top < 0 || n_choices < 1)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_vote_from_logprobs: bad shape (rows=%d top=%d choices=%d)", n_rows, n_top,
+                    n_choices);
+    if (n_rows == 0) return LWC_OK;
+    if (!V || (n_top > 0 && (!logprob || !leaf))) return fail(ctx, LWC_ERR_INVALID, "lwc_vote_from_logprobs: NULL argument");
+    if (memory != LWC_MEM_HOST && memory != LWC_MEM_DEVICE)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_vote_from_logprobs: memory must be LWC_MEM_HOST or LWC_MEM_DEVICE");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = (memory == LWC_MEM_DEVICE && stream) ? static_cast<cudaStream_t>(stream) : ctx->stream;
+    const float *dlp = logprob;
+    const int32_t *dlf = leaf;
+    float *dV = V;
+    const size_t in_bytes = (size_t)n_rows * n_top * 4, out_bytes = (size_t)n_rows * n_choices * 4;
+    if (memory == LWC_MEM_HOST) {
+        Slot &s = ctx->slots[0];
+        int rc;
+        if ((rc = ensure(ctx, s, 0, in_bytes + 4))) return rc;
+        if ((rc = ensure(ctx, s, 1, in_bytes + 4))) return rc;
+        if ((rc = ensure(ctx, s, 3, out_bytes))) return rc;
+        if (in_bytes) {
+            CUDA_TRY(ctx, cudaMemcpyAsync(s.buf[0], logprob, in_bytes, cudaMemcpyHostToDevice, st));
+            CUDA_TRY(ctx, cudaMemcpyAsync(s.buf[1], leaf, in_bytes, cudaMemcpyHostToDevice, st));
+        }
+        dlp = static_cast<const float *>(s.buf[0]);
+        dlf = static_cast<const int32_t *>(s.buf[1]);
+        dV = static_cast<float *>(s.buf[3]);
+    }
+    const int warps = 4;
+    lwc::vote_from_logprobs_kernel<<<(n_rows + warps - 1) / warps, warps * 32, 0, st>>>(dlp, dlf, dV, n_rows, n_top,
+                                                                                     n_choices);
+    CUDA_TRY(ctx, cudaGetLastError());
+    ctx->launches++;
+    if (memory == LWC_MEM_HOST) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(V, dV, out_bytes, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    }
+    return LWC_OK;
 }
 
 int32_t lwc_stage_f64(lwc_ctx *ctx, const double *src, size_t n, float *dst) {

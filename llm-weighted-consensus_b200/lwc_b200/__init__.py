@@ -75,6 +75,8 @@ def load_library():
     L.lwc_launch_count.restype = u64
     L.lwc_merge_error_codes.argtypes = [ctypes.POINTER(ctypes.c_uint16), i32]
     L.lwc_merge_error_codes.restype = i32
+    L.lwc_vote_from_logprobs.argtypes = [vp, i32, i32, i32, vp, vp, vp, i32, vp]
+    L.lwc_vote_from_logprobs.restype = i32
     L.lwc_stage_f64.argtypes = [vp, vp, ctypes.c_size_t, vp]
     L.lwc_stage_f64.restype = i32
     _lib = L
@@ -244,6 +246,16 @@ class Context:
         finally:
             for b in bufs:
                 b.free()
+
+    def vote_from_logprobs(self, logprob, leaf, n_choices):
+        """Host-memory call of lwc_vote_from_logprobs: [rows, top] logprobs + leaf indices -> [rows, n_choices]."""
+        lp = np.ascontiguousarray(logprob, dtype=np.float32)
+        lf = np.ascontiguousarray(leaf, dtype=np.int32)
+        rows, top = lp.shape
+        V = np.full((rows, n_choices), -7.0, np.float32)
+        self._check(self.lib.lwc_vote_from_logprobs(self.handle, rows, top, n_choices, _np_ptr(lp), _np_ptr(lf),
+                                                    _np_ptr(V), MEM_HOST, None))
+        return V
 
     def stage_f64(self, src, dst):
         src = np.ascontiguousarray(src, dtype=np.float64)

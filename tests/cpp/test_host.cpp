@@ -1,0 +1,157 @@
+// test_host.cpp -- exercises llm-weighted-consensus_b200/host/lwc_host.hpp.
+//   ./test_host            CPU box: type mirror + error mapping (no device -> ResponseError 503), K2 merge
+//   ./test_host --gpu      B200: 8 threads submit 400 mixed-shape requests through the Batcher; every
+//                          result must equal a single-request lwc_score_batch call bit for bit
+#include <atomic>
+#include <numeric>
+#include <cstdio>
+#include <random>
+
+#include "../../llm-weighted-consensus_b200/host/lwc_host.hpp"
+
+using namespace lwc;
+using score::completions::Request;
+using score::completions::Tally;
+using score::completions::VoterChoice;
+
+#define REQUIRE(c)                                                        \
+    do {                                                                  \
+        if (!(c)) {                                                       \
+            std::printf("FAILED %s:%d: %s\n", __FILE__, __LINE__, #c);    \
+            return 1;                                                     \
+        }                                                                 \
+    } while (0)
+
+static int cpu_checks() {
+    // client.rs:390-408 through the host types (golden K2)
+    std::vector<VoterChoice> v(2);
+    v[0].error_code = 429, v[1].error_code = 429;
+    REQUIRE(merge_error_codes(v).value() == 429);
+    v[0].error_code = 400;
+    REQUIRE(merge_error_codes(v).value() == 400);
+    v[1].error_code = 500;
+    REQUIRE(merge_error_codes(v).value() == 500);
+    v[1].error_code.reset(); // a voter without an error: not an all-failed request
+    REQUIRE(!merge_error_codes(v).has_value());
+    REQUIRE(merge_error_codes({}).value() == 500); // AllVotesFailed(None) -> 500 (error.rs:41)
+    return 0;
+}
+
+static int no_device_check() {
+    try {
+        Context c(0);
+    } catch (const error::ResponseError &e) {
+        REQUIRE(e.code == 503);
+        REQUIRE(e.message.find("no CPU path") != std::string::npos);
+        std::printf("no device: %s\n", e.what());
+        return 0;
+    }
+    std::printf("a CUDA device is present; skipping the no-device check\n");
+    return 0;
+}
+
+static int gpu_checks() {
+    Batcher::Options opt;
+    opt.max_wait_us = 500;
+    Batcher batcher(0, opt);
+    const int shapes[3][3] = {{16, 1536, 4}, {5, 64, 3}, {32, 256, 7}};
+    const int T = 8, PER = 50;
+    std::vector<std::vector<Request>> reqs(T);
+    std::vector<std::vector<embeddings::response::CreateEmbeddingResponse>> embs(T);
+    std::vector<std::vector<Tally>> got(T);
+    for (int t = 0; t < T; ++t) {
+        std::mt19937 g(100 + t);
+        std::normal_distribution<double> nd;
+        std::uniform_real_distribution<double> ud(0.0, 1.0);
+        embs[t].resize(PER);
+        reqs[t].resize(PER);
+        for (int i = 0; i < PER; ++i) {
+            const int *s = shapes[(t + i) % 3];
+            const int N = s[0], D = s[1], M = s[2];
+            auto &er = embs[t][i];
+            er.data.resize(N);
+            for (int n = 0; n < N; ++n) {
+                er.data[n].index = (uint64_t)((n * 7 + 3) % N); // scrambled arrival order, as over the wire
+                if (std::gcd(7, N) != 1) er.data[n].index = n;
+                er.data[n].embedding.resize(D);
+                for (auto &x : er.data[n].embedding) x = nd(g);
+            }
+            Request &rq = reqs[t][i];
+            rq.n_choices = N;
+            rq.embeddings = (i % 5 == 4) ? nullptr : &er; // some pure-tally requests (similarity = identity)
+            rq.voters.resize(M);
+            for (int m = 0; m < M; ++m) {
+                if (ud(g) < 0.1) continue; // voter without a vote
+                std::vector<double> vote(N);
+                double sum = 0;
+                for (auto &x : vote) sum += (x = ud(g));
+                for (auto &x : vote) x /= sum;
+                rq.voters[m].vote = vote;
+                if (ud(g) > 0.05) rq.voters[m].weight = 0.5 + 1.5 * ud(g);
+            }
+        }
+    }
+    std::vector<std::thread> th;
+    std::atomic<int> failures{0};
+    for (int t = 0; t < T; ++t)
+        th.emplace_back([&, t] {
+            std::vector<std::future<Tally>> f;
+            for (auto &rq : reqs[t]) f.push_back(batcher.submit(rq));
+            for (auto &x : f) {
+                try {
+                    got[t].push_back(x.get());
+                } catch (const std::exception &e) {
+                    std::printf("request failed: %s\n", e.what());
+                    ++failures;
+                }
+            }
+        });
+    for (auto &x : th) x.join();
+    REQUIRE(failures == 0);
+    std::printf("batches launched: %llu for %d requests\n", (unsigned long long)batcher.batches(), T * PER);
+    REQUIRE(batcher.batches() < (uint64_t)T * PER); // requests were actually batched
+
+    // every batched result == the same request alone through the Batcher's own context
+    Batcher solo(0);
+    for (int t = 0; t < T; ++t)
+        for (int i = 0; i < PER; ++i) {
+            Tally a = solo.submit(reqs[t][i]).get();
+            const Tally &b = got[t][i];
+            REQUIRE(a.winner == b.winner);
+            REQUIRE(a.rank == b.rank);
+            REQUIRE(a.weight.size() == b.weight.size());
+            for (size_t k = 0; k < a.weight.size(); ++k) {
+                REQUIRE(a.weight[k] == b.weight[k]);
+                REQUIRE(a.confidence[k] == b.confidence[k]);
+            }
+            for (size_t m = 0; m < a.voter_confidence.size(); ++m) {
+                REQUIRE(a.voter_confidence[m].has_value() == b.voter_confidence[m].has_value());
+                REQUIRE(a.voter_confidence[m].has_value() == reqs[t][i].voters[m].vote.has_value());
+                if (a.voter_confidence[m]) REQUIRE(*a.voter_confidence[m] == *b.voter_confidence[m]);
+            }
+            double s = 0;
+            for (double c : b.confidence) s += c;
+            if (b.winner >= 0) {
+                REQUIRE(std::fabs(s - 1.0) < 1e-5);
+                REQUIRE(b.rank[0] == b.winner);
+            }
+        }
+    // argument errors surface as ResponseError 400, like Error::ExpectedTwoOrMoreChoices would
+    try {
+        Request bad;
+        bad.n_choices = 0;
+        batcher.submit(bad);
+        REQUIRE(false);
+    } catch (const error::ResponseError &e) {
+        REQUIRE(e.code == 400);
+    }
+    return 0;
+}
+
+int main(int argc, char **argv) {
+    const bool gpu = argc > 1 && std::string(argv[1]) == "--gpu";
+    if (cpu_checks()) return 1;
+    if (gpu ? gpu_checks() : no_device_check()) return 1;
+    std::printf("OK\n");
+    return 0;
+}

@@ -287,3 +287,27 @@ def test_stage_f64(ctx, lwc):
     dst = np.empty(1000, np.float32)
     ctx.stage_f64(src, dst)
     assert np.array_equal(dst, src.astype(np.float32))
+
+
+def test_vote_from_logprobs(ctx, lwc, oracle):
+    """the numeric tail of get_vote (client.rs:1765-1791) on device.  The reference's
+    Decimal::exp is a truncated series (~1e-7); fp32 expf is compared to f64 exp at 1e-5 relative."""
+    rng = np.random.default_rng(21)
+    rows, top, n = 300, 20, 37
+    lp = rng.normal(-2.0, 2.0, (rows, top)).astype(np.float32)
+    leaf = rng.integers(-1, n, (rows, top)).astype(np.int32)
+    lp[5, 3] = np.nan          # logprob None
+    leaf[7] = -1               # no admissible alternative -> the reference's unreachable!(): absent voter
+    V = ctx.vote_from_logprobs(lp, leaf, n)
+    for r in range(rows):
+        if r == 7:
+            assert np.all(np.isnan(V[r]))
+            continue
+        want = oracle.vote_from_logprobs(n, lp[r].astype(np.float64), leaf[r])
+        np.testing.assert_allclose(V[r], want, rtol=1e-5, atol=1e-8)
+        assert abs(V[r].sum() - 1.0) < 1e-5
+    # the rows feed the scorer directly: one-hot-like votes must keep the winner
+    E = rng.standard_normal((1, n, 64)).astype(np.float32)
+    got = ctx.score_batch(E, V[None, :4], np.ones((1, 4), np.float32))
+    want = oracle.score_f64(E, V[None, :4], np.ones((1, 4), np.float32))
+    assert got["winner"][0] == want["winner"][0]
