@@ -18,6 +18,7 @@
 #include "score_generic.cuh"
 #include "score_small.cuh"
 #include "score_stream.cuh"
+#include "score_tc.cuh"
 #include "vote_kernel.cuh"
 
 #define LWC_VERSION_STRING "lwc_b200 0.1.0 (sm_100a)"
@@ -56,6 +57,8 @@ struct lwc_ctx {
     int stream_slots = 0; // ring depth override (LWC_STREAM_SLOTS)
     int stream_nf = 0;    // finaliser warps, 0 = 1 (LWC_STREAM_NF)
     int max_smem_optin = 0;
+    int tc_ko = 0;     // operand slabs per stage of the tcgen05 kernel (LWC_TC_KO)
+    int tc_stages = 0; // its ring depth (LWC_TC_STAGES)
 };
 
 namespace {
@@ -83,7 +86,7 @@ int fail(lwc_ctx *ctx, int code, const char *fmt, ...) {
                         __FILE__, __LINE__);                                                             \
     } while (0)
 
-enum Route { ROUTE_INVALID = 0, ROUTE_GENERIC, ROUTE_SMALL };
+enum Route { ROUTE_INVALID = 0, ROUTE_GENERIC, ROUTE_SMALL, ROUTE_TC };
 
 struct Plan {
     Route route = ROUTE_INVALID;
@@ -112,6 +115,14 @@ Plan plan_for(const lwc_batch_desc &d, const void *E) {
         pl.np = d.N <= 16 ? 16 : 32;
         pl.x3 = (d.precision == LWC_PREC_FP32 || d.precision == LWC_PREC_TF32X3);
         pl.name = pl.np == 16 ? (pl.x3 ? "small16_tf32x3" : "small16_tf32") : (pl.x3 ? "small32_tf32x3" : "small32_tf32");
+        return pl;
+    }
+    // large pools: the similarity on tcgen05 tensor cores when the caller accepts TF32-grade inputs
+    if (d.N > 32 && aligned && d.D % 32 == 0 && (d.precision == LWC_PREC_TF32 || d.precision == LWC_PREC_BF16)) {
+        pl.route = ROUTE_TC;
+        pl.np = 128;
+        pl.x3 = false;
+        pl.name = "tc128_tf32";
         return pl;
     }
     pl.route = ROUTE_GENERIC;
@@ -200,6 +211,43 @@ EncodeTiledFn encode_tiled_fn() {
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// E viewed as a rank-4 fp32 tensor {32 (k_in), N (row), D/32 (k_out), R}: one box {32, 128, ko, 1} lands as
+// ko K-major SWIZZLE_128B operand slabs of [128 rows x 128 B] (score_tc.cuh).
+bool make_tensor_map_tc(CUtensorMap *tm, const float *E, int R, int N, int D, int ko) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) return false;
+    cuuint64_t dims[4] = {32, (cuuint64_t)N, (cuuint64_t)(D / 32), (cuuint64_t)R};
+    cuuint64_t strides[3] = {(cuuint64_t)D * 4, 128, (cuuint64_t)N * D * 4};
+    cuuint32_t box[4] = {32, 128, (cuuint32_t)ko, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    return fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float *>(E), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
+    lwc::TcGeom geo;
+    geo.ko = ctx->tc_ko > 0 ? ctx->tc_ko : 4; // 64 KB boxes x 3 stages streamed fastest (profiles/r1_tma_probe2.txt)
+    const int nslab = p.D / 32;
+    if (geo.ko > nslab) geo.ko = nslab;
+    geo.stages = lwc::kTcMaxStages;
+    while (geo.stages > 1 && lwc::tc_smem_bytes(geo.ko, geo.stages) > (size_t)ctx->max_smem_optin) --geo.stages;
+    if (ctx->tc_stages > 0 && ctx->tc_stages < geo.stages) geo.stages = ctx->tc_stages;
+    if (lwc::tc_smem_bytes(geo.ko, geo.stages) > (size_t)ctx->max_smem_optin) return cudaErrorInvalidConfiguration;
+    static bool configured[64] = {false};
+    if (!configured[ctx->device & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             ctx->max_smem_optin);
+        if (e != cudaSuccess) return e;
+        configured[ctx->device & 63] = true;
+    }
+    CUtensorMap tm;
+    if (!make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, geo.ko)) return cudaErrorInvalidValue;
+    const int grid = p.R < ctx->sm_count ? p.R : ctx->sm_count;
+    lwc::score_tc_kernel<<<grid, lwc::kTcThreads, lwc::tc_smem_bytes(geo.ko, geo.stages), st>>>(tm, p, geo);
+    return cudaGetLastError();
+}
+
 template <int NT, bool X3, int NCW, int NF>
 cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
     using C = lwc::StreamCfg<NT, X3, NCW, NF>;
@@ -253,7 +301,9 @@ int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStr
     // 32-candidate pools with the compensated 3xTF32 Gram are bound by the legacy mma.sync pipe, not by
     // HBM; there the one-CTA-per-request kernel (more warps in flight) measured 83 % vs 80 % of HBM peak.
     const bool stream_route = ctx->small_impl == 0 && !(pl.np == 32 && pl.x3 && !ctx->force_stream);
-    if (pl.route == ROUTE_SMALL && stream_route) {
+    if (pl.route == ROUTE_TC) {
+        e = launch_tc(ctx, p, st);
+    } else if (pl.route == ROUTE_SMALL && stream_route) {
         if (pl.np == 16)
             e = pl.x3 ? launch_stream<16, true>(ctx, p, st) : launch_stream<16, false>(ctx, p, st);
         else
@@ -421,6 +471,8 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     if (const char *s = getenv("LWC_STREAM_KC")) ctx->stream_kc = atoi(s);
     if (const char *s = getenv("LWC_STREAM_SLOTS")) ctx->stream_slots = atoi(s);
     if (const char *s = getenv("LWC_STREAM_NF")) ctx->stream_nf = atoi(s);
+    if (const char *s = getenv("LWC_TC_KO")) ctx->tc_ko = atoi(s);
+    if (const char *s = getenv("LWC_TC_STAGES")) ctx->tc_stages = atoi(s);
     if (ctx->stream_ncw != 0 && ctx->stream_ncw != 4 && ctx->stream_ncw != 8 && ctx->stream_ncw != 12) ctx->stream_ncw = 0;
     if (ctx->stream_kc < 0 || ctx->stream_kc % 16) ctx->stream_kc = 0;
     cudaDeviceGetAttribute(&ctx->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);

@@ -1,0 +1,313 @@
+// score_tc.cuh -- large-pool scoring kernel (32 < N <= 128): the similarity matrix on the 5th-gen
+// tensor cores (tcgen05.mma kind::tf32, fp32 accumulate in TMEM), sm_100a.
+//
+// One persistent CTA per SM, each owning a contiguous range of requests; per request the whole
+// pool is ONE 128 x 128 UMMA tile: S = E E^T with A = B = the request's [N][D] tile.
+//
+//   warp 0 (1 lane)  TMA producer.  E is described as a rank-4 fp32 tensor {32, N, D/32, R}
+//                    (k_in, row, k_out, request); one cp.async.bulk.tensor.4d moves a box
+//                    {32, 128, KO, 1} = KO operand slabs of [128 rows x 128 B], 128-byte swizzled,
+//                    i.e. exactly the K-major SWIZZLE_128B canonical layout UMMA reads.  Rows >= N
+//                    are out of bounds and arrive as zeros.  tools/tma_probe2.cu
+//                    (profiles/r1_tma_probe2.txt): 32 KB boxes x 4 stages stream at 6.0 TB/s,
+//                    64 KB boxes x 3 stages at 6.58 TB/s.
+//   warp 1 (1 lane)  MMA issuer.  Per slab 4 x tcgen05.mma (M=128, N=128, K=8), the SAME shared
+//                    tile as A and as B descriptor; tcgen05.commit releases the stage; the last
+//                    commit of a request signals the epilogue.  Two 128-column accumulators in
+//                    TMEM alternate, so request q+1 accumulates while q is being finalised.
+//   warps 4..7       epilogue: thread i owns TMEM lane i = row i of S (tcgen05.ld 32x32b).
+//                    n_i^2 = S_ii; u_i = t_i / n_i goes to shared memory; because S is symmetric,
+//                    cw_i = (1/n_i) * sum_j u_j S_ij needs only the thread's own row.  Then the
+//                    tally of client.rs:422-449 with block reductions, argmax and rank.
+//
+// Inputs are read by the tensor core as TF32 (the low 13 mantissa bits of each fp32 are ignored):
+// this is the `precision = LWC_PREC_TF32` route with the stated 2e-3 confidence tolerance.
+// Bound: HBM (64 flop/B at N = 128 against a TF32 balance of > 150 flop/B).
+#pragma once
+
+#include <cuda.h>
+
+#include "score_stream.cuh"
+
+namespace lwc {
+
+constexpr int kTcThreads = 256;
+constexpr int kTcSlabBytes = 128 * 128;  // one [128 rows x 32 fp32] operand slab, SWIZZLE_128B
+constexpr int kTcMaxStages = 8;
+
+struct TcGeom {
+    int ko;     // operand slabs (32 columns each) per TMA box / pipeline stage
+    int stages; // ring depth
+};
+
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *tm, int c0, int c1, int c2, int c3,
+                                            uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+        ::"r"(dst), "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
+        : "memory");
+}
+
+// K-major SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
+// start address >> 4 | LBO (=1, unused for swizzled K-major) << 16 | SBO (1024 B between 8-row
+// groups) >> 4 << 32 | version 1 << 46 | layout SWIZZLE_128B (2) << 61.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) |
+           (2ull << 61);
+}
+
+// Instruction descriptor: D = F32 (1<<4), A = B = TF32 (2<<7, 2<<10), both K-major, N>>3 at bit 17, M>>4 at bit 24.
+__device__ __forceinline__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// All MMAs issued so far by this thread arrive on `bar` when they complete (implies fence::before_thread_sync).
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// 32 consecutive accumulator columns of this thread's TMEM lane.
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// named barrier over the 128 epilogue threads only
+__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+__global__ void __launch_bounds__(kTcThreads, 1)
+score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, const TcGeom geo) {
+    extern __shared__ __align__(1024) unsigned char smem_tc[];
+    const int KO = geo.ko, S = geo.stages;
+    const int stageb = KO * kTcSlabBytes;
+    // dynamic shared memory is only guaranteed 16-byte aligned: SWIZZLE_128B tiles need 1024
+    unsigned char *ring = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_tc) + 1023) & ~(uintptr_t)1023);
+    float *u_s = reinterpret_cast<float *>(ring + (size_t)S * stageb); // [128] t_i / n_i
+    float *cf_s = u_s + 128;                                          // [128] confidences
+    float *part = cf_s + 128;                                         // [16] block-reduction scratch
+    int *ipart = reinterpret_cast<int *>(part + 16);                  // [8]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(ipart + 8);    // [2]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(tmem_slot + 2);     // full[S], empty[S], tfull[2], tempty[2]
+    const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * kTcMaxStages;
+    const uint32_t tfull0 = empty0 + 8 * kTcMaxStages, tempty0 = tfull0 + 16;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int N = p.N, D = p.D, M = p.M;
+    const int r_begin = (int)(((long long)blockIdx.x * p.R) / gridDim.x);
+    const int r_end = (int)(((long long)(blockIdx.x + 1) * p.R) / gridDim.x);
+    const int nreq = r_end - r_begin;
+    const int nslab = D >> 5;                  // 32-column operand slabs per request (D % 32 == 0)
+    const int spr = (nslab + KO - 1) / KO;     // stages per request
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < S; ++s) {
+            mbar_init(full0 + 8 * s, 1);
+            mbar_init(empty0 + 8 * s, 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(tfull0 + 8 * b, 1);
+            mbar_init(tempty0 + 8 * b, 128);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) { // TMEM: 256 columns = two 128 x 128 fp32 accumulators
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            const uint32_t ring_u32 = smem_u32(ring);
+            int slot = 0;
+            uint32_t phase = 0;
+            for (int q = 0; q < nreq; ++q)
+                for (int s = 0; s < spr; ++s) {
+                    mbar_wait(empty0 + 8 * slot, phase ^ 1u);
+                    mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)stageb); // OOB zero-fill counts too
+                    tma_load_4d(ring_u32 + slot * stageb, &tmE, 0, 0, s * KO, r_begin + q, full0 + 8 * slot);
+                    if (++slot == S) {
+                        slot = 0;
+                        phase ^= 1u;
+                    }
+                }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t ring_u32 = smem_u32(ring);
+            const uint32_t idesc = umma_idesc_tf32(128, 128);
+            int slot = 0;
+            uint32_t phase = 0;
+            for (int q = 0; q < nreq; ++q) {
+                const int ab = q & 1;
+                mbar_wait(tempty0 + 8 * ab, (((uint32_t)q >> 1) & 1u) ^ 1u); // accumulator drained by the epilogue
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(ab * 128);
+                uint32_t acc = 0;
+                for (int s = 0; s < spr; ++s) {
+                    mbar_wait(full0 + 8 * slot, phase);
+                    tc_fence_after();
+                    const int nk = min(KO, nslab - s * KO);
+                    for (int k = 0; k < nk; ++k) {
+                        const uint32_t slab = ring_u32 + slot * stageb + k * kTcSlabBytes;
+#pragma unroll
+                        for (int kk = 0; kk < 4; ++kk) { // 4 x K=8 inside the 128-byte swizzle atom
+                            const uint64_t desc = umma_desc_sw128(slab + kk * 32);
+                            umma_tf32(d_tmem, desc, desc, idesc, acc);
+                            acc = 1;
+                        }
+                    }
+                    umma_commit(empty0 + 8 * slot); // stage reusable once these MMAs have read it
+                    if (++slot == S) {
+                        slot = 0;
+                        phase ^= 1u;
+                    }
+                }
+                umma_commit(tfull0 + 8 * ab); // accumulator complete
+            }
+        }
+        __syncwarp();
+    } else if (warp >= 4) {
+        // ===================== epilogue =====================
+        const int i = threadIdx.x - 128;   // row of S owned by this thread == TMEM lane
+        const int ew = warp - 4;           // TMEM lane quarter this warp may access
+        const bool act = i < N;
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
+        for (int q = 0; q < nreq; ++q) {
+            const int r = r_begin + q, ab = q & 1;
+            const float *Vr = p.V + (size_t)r * M * N;
+            const float *wr = p.w + (p.w_per_request ? (size_t)r * M : 0);
+            // t_i = sum_m w_m V_mi (client.rs:410-415): independent of E, overlaps the MMAs
+            float t = 0.f;
+            for (int m = 0; m < M; ++m) {
+                const float v0 = __ldg(Vr + (size_t)m * N);
+                if (isnan(v0)) continue;
+                float wm = __ldg(wr + m);
+                if (isnan(wm)) wm = 0.f;
+                if (act) t = fmaf(__ldg(Vr + (size_t)m * N + i), wm, t);
+            }
+            mbar_wait(tfull0 + 8 * ab, ((uint32_t)q >> 1) & 1u);
+            tc_fence_after();
+            const uint32_t row_addr = lane_addr + (uint32_t)(ab * 128);
+            float v[32];
+            // diagonal: S_ii sits in column chunk `ew` at register index `lane`
+            tmem_ld32(row_addr + (uint32_t)(ew * 32), v);
+            float d = 0.f;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) d = (lane == e) ? v[e] : d;
+            const float rn = (act && d > 0.f) ? 1.0f / sqrtf(d) : 0.f;
+            u_s[i] = t * rn;
+            epi_sync();
+            float acc = 0.f;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                tmem_ld32(row_addr + (uint32_t)(c * 32), v);
+#pragma unroll
+                for (int e = 0; e < 32; ++e) acc = fmaf(u_s[c * 32 + e], v[e], acc);
+            }
+            // accumulator fully read: hand it back to the MMA warp
+            tc_fence_before();
+            mbar_arrive(tempty0 + 8 * ab);
+            float c = act ? acc * rn : 0.f;
+            // ---- tally (client.rs:422-449) with fixed-order block reductions
+            float ws = warp_sum(c);
+            if (lane == 0) part[ew] = ws;
+            epi_sync();
+            const float sum = (part[0] + part[1]) + (part[2] + part[3]);
+            const bool positive = sum > 0.f;
+            const float cf = (positive && act) ? c / sum : 0.f;
+            cf_s[i] = cf;
+            if (act) {
+                if (p.cw) p.cw[(size_t)r * N + i] = c;
+                if (p.conf) p.conf[(size_t)r * N + i] = cf;
+            }
+            if (p.winner) {
+                float bv = act ? cf : -1.f;
+                int bi = act ? i : 0x7fffffff;
+                warp_argmax(bv, bi);
+                if (lane == 0) {
+                    part[4 + ew] = bv;
+                    ipart[ew] = bi;
+                }
+            }
+            epi_sync();
+            if (p.winner && i == 0) {
+                float best = part[4];
+                int besti = ipart[0];
+#pragma unroll
+                for (int k = 1; k < 4; ++k)
+                    if (part[4 + k] > best || (part[4 + k] == best && ipart[k] < besti)) {
+                        best = part[4 + k];
+                        besti = ipart[k];
+                    }
+                p.winner[r] = positive ? besti : -1;
+            }
+            if (p.rank && act) {
+                int pos = 0;
+                for (int j = 0; j < N; ++j) {
+                    const float cj = cf_s[j];
+                    pos += (cj > cf || (cj == cf && j < i)) ? 1 : 0;
+                }
+                p.rank[(size_t)r * N + pos] = i;
+            }
+            if (p.agree) {
+                for (int m = ew; m < M; m += 4) { // one warp per voter
+                    const float v0 = __ldg(Vr + (size_t)m * N);
+                    float a;
+                    if (isnan(v0)) {
+                        a = __int_as_float(0x7fc00000);
+                    } else {
+                        float s = 0.f;
+                        for (int j = lane; j < N; j += 32) s = fmaf(cf_s[j], __ldg(Vr + (size_t)m * N + j), s);
+                        a = warp_sum(s);
+                    }
+                    if (lane == 0) p.agree[(size_t)r * M + m] = a;
+                }
+            }
+            epi_sync(); // u_s / cf_s / part are reused by the next request
+        }
+    }
+
+    // ---- teardown: everyone done with TMEM before it is freed
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256) : "memory");
+    }
+}
+
+inline size_t tc_smem_bytes(int ko, int stages) {
+    return 1024 + (size_t)stages * ko * kTcSlabBytes + (128 + 128 + 16 + 8 + 2) * 4 + (2 * kTcMaxStages + 4) * 8 + 64;
+}
+
+} // namespace lwc
