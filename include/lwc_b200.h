@@ -21,6 +21,9 @@
  *   lwc_stage_f64 .......... the Vec<f64> -> device fp32 hop for
  *                            embeddings::response::Embedding.embedding
  *                            (src/embeddings/response.rs:19-24).
+ *   lwc_pool_consensus ..... client.rs:384-456 for ONE request whose pool is too large for a
+ *                            batch slot (BASELINE.json config 5: 262,144 candidates), rows
+ *                            sharded over the GPUs of a node; no other reference counterpart.
  *   lwc_vote_from_logprobs . the numeric tail of get_vote, client.rs:1765-1791: exp(logprob) of
  *                            the sibling-leaf alternatives, accumulated per choice, divided by
  *                            the probability sum.
@@ -154,6 +157,33 @@ int32_t lwc_stage_f64(lwc_ctx *ctx, const double *src, size_t n, float *dst);
  * `memory` as in lwc_batch_desc; device calls are asynchronous on `stream`. */
 int32_t lwc_vote_from_logprobs(lwc_ctx *ctx, int32_t n_rows, int32_t n_top, int32_t n_choices, const float *logprob,
                                const int32_t *leaf, float *V, int32_t memory, void *stream);
+
+/* ---- one giant pool (all-pairs consensus), optionally row-sharded over the ranks of a node ---- */
+
+typedef struct {
+    int64_t N;         /* candidate rows THIS rank holds (every rank must hold the same number) */
+    int32_t D;         /* embedding dimension, D % 8 == 0 */
+    int32_t M;         /* voters, 0..LWC_MAX_VOTERS */
+    int32_t precision; /* LWC_PREC_BF16: normalised rows are rounded to bf16 for the tcgen05 pass
+                          (confidences within 1e-2 of the top confidence); other values -> 400 */
+    int32_t memory;    /* LWC_MEM_* for every pointer below */
+} lwc_pool_desc;
+
+/* replaces: client.rs:384-456 applied to one request of N * nranks candidates.
+ *   E [N][D] own rows; V [M][N] the vote entries of own rows (a voter without a vote: NaN row on every
+ *   rank); w [M].  Outputs: conf, cw [N] for own rows; agree [M] and *winner (global row index, -1 if
+ *   the weight sum is not > 0) identical on every rank.  rank order is not produced for a pool.
+ * With a communicator attached (lwc_comm_init) the normalised rows and the tally vector are
+ * all-gathered over NVLink (NCCL) -- the path's only exchange step -- and three scalars per rank are
+ * reduced; without one the call is single-GPU.  Blocking: returns with outputs written. */
+int32_t lwc_pool_consensus(lwc_ctx *ctx, const lwc_pool_desc *desc, const float *E, const float *V, const float *w,
+                           float *conf, float *cw, float *agree, int64_t *winner, void *stream);
+
+/* NCCL plumbing for the sharded pool: rank 0 creates a 128-byte id, every rank calls lwc_comm_init
+ * with it (collective).  NCCL is loaded with dlopen("libnccl.so.2") on first use; 503 if absent. */
+int32_t lwc_comm_unique_id(void *id128);
+int32_t lwc_comm_init(lwc_ctx *ctx, int32_t nranks, int32_t rank, const void *id128);
+int32_t lwc_comm_destroy(lwc_ctx *ctx);
 
 #ifdef __cplusplus
 }

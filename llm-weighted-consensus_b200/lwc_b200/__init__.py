@@ -32,6 +32,11 @@ class BatchDesc(ctypes.Structure):
                 ("R", "N", "D", "M", "similarity", "precision", "memory", "w_per_request")]
 
 
+class PoolDesc(ctypes.Structure):
+    _fields_ = [("N", ctypes.c_int64), ("D", ctypes.c_int32), ("M", ctypes.c_int32), ("precision", ctypes.c_int32),
+                ("memory", ctypes.c_int32)]
+
+
 class Config(ctypes.Structure):
     _fields_ = [("device", ctypes.c_int32), ("chunk_requests", ctypes.c_int32), ("reserved", ctypes.c_uint64 * 4)]
 
@@ -77,6 +82,14 @@ def load_library():
     L.lwc_merge_error_codes.restype = i32
     L.lwc_vote_from_logprobs.argtypes = [vp, i32, i32, i32, vp, vp, vp, i32, vp]
     L.lwc_vote_from_logprobs.restype = i32
+    L.lwc_pool_consensus.argtypes = [vp, ctypes.POINTER(PoolDesc)] + [vp] * 8
+    L.lwc_pool_consensus.restype = i32
+    L.lwc_comm_unique_id.argtypes = [vp]
+    L.lwc_comm_unique_id.restype = i32
+    L.lwc_comm_init.argtypes = [vp, i32, i32, vp]
+    L.lwc_comm_init.restype = i32
+    L.lwc_comm_destroy.argtypes = [vp]
+    L.lwc_comm_destroy.restype = i32
     L.lwc_stage_f64.argtypes = [vp, vp, ctypes.c_size_t, vp]
     L.lwc_stage_f64.restype = i32
     _lib = L
@@ -86,6 +99,15 @@ def load_library():
 def merge_error_codes(codes) -> int:
     arr = (ctypes.c_uint16 * max(len(codes), 1))(*codes)
     return load_library().lwc_merge_error_codes(arr, len(codes))
+
+
+def comm_unique_id() -> bytes:
+    """128-byte NCCL id for lwc_comm_init; create on rank 0 and broadcast (e.g. torch.distributed)."""
+    buf = ctypes.create_string_buffer(128)
+    rc = load_library().lwc_comm_unique_id(buf)
+    if rc:
+        raise LwcError(rc, load_library().lwc_last_error_message(None).decode())
+    return buf.raw
 
 
 def version() -> str:
@@ -246,6 +268,30 @@ class Context:
         finally:
             for b in bufs:
                 b.free()
+
+    def comm_init(self, nranks, rank, unique_id: bytes):
+        buf = ctypes.create_string_buffer(unique_id, 128)
+        self._check(self.lib.lwc_comm_init(self.handle, nranks, rank, buf))
+
+    def comm_destroy(self):
+        self._check(self.lib.lwc_comm_destroy(self.handle))
+
+    def pool_consensus(self, E, V, w, precision=PREC_BF16):
+        """Host-memory call of lwc_pool_consensus on this rank's rows: E [N,D], V [M,N], w [M]."""
+        E = np.ascontiguousarray(E, dtype=np.float32)
+        V = np.ascontiguousarray(V, dtype=np.float32)
+        w = np.ascontiguousarray(w, dtype=np.float32)
+        N, D = E.shape
+        M = V.shape[0]
+        desc = PoolDesc(N, D, M, precision, MEM_HOST)
+        conf = np.full((N,), np.nan, np.float32)
+        cw = np.full((N,), np.nan, np.float32)
+        agree = np.full((max(M, 1),), -7.0, np.float32)
+        winner = ctypes.c_int64(-9)
+        self._check(self.lib.lwc_pool_consensus(self.handle, ctypes.byref(desc), _np_ptr(E), _np_ptr(V), _np_ptr(w),
+                                                _np_ptr(conf), _np_ptr(cw), _np_ptr(agree),
+                                                ctypes.cast(ctypes.byref(winner), ctypes.c_void_p), None))
+        return {"conf": conf, "cw": cw, "agree": agree[:M], "winner": int(winner.value)}
 
     def vote_from_logprobs(self, logprob, leaf, n_choices):
         """Host-memory call of lwc_vote_from_logprobs: [rows, top] logprobs + leaf indices -> [rows, n_choices]."""
