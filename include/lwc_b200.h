@@ -179,6 +179,33 @@ typedef struct {
 int32_t lwc_pool_consensus(lwc_ctx *ctx, const lwc_pool_desc *desc, const float *E, const float *V, const float *w,
                            float *conf, float *cw, float *agree, int64_t *winner, void *stream);
 
+/* No counterpart in the reference: this entry point exists for hosts that must not allocate.
+ * A serving process that has given all of a GPU's memory to its own pool, or whose scoring thread may
+ * not take the driver's allocation lock (cudaMalloc/cudaFree synchronise the whole device and would
+ * stall every other stream, e.g. the batcher threads of the other requests), can still score one pool
+ * with this call.  It is lwc_pool_consensus for a single GPU with every pointer in DEVICE memory
+ * (desc->memory must be LWC_MEM_DEVICE, no communicator attached, `winner` is a device int64), and it
+ * takes its working memory from a fixed array that lives inside the library's device image instead of
+ * from cudaMalloc: LWC_STATIC_SCRATCH_BYTES per GPU, held from the moment the library is loaded on
+ * that GPU until the process exits, whether or not this function is ever called.
+ *   Limits: N <= LWC_STATIC_POOL_MAX_ROWS and N * D <= LWC_STATIC_POOL_MAX_ELEMS; anything larger is
+ *   refused with 400 and a message naming the limit (use lwc_pool_consensus then).
+ *   The call makes no cudaMalloc/cudaFree or other allocating call.  It is asynchronous on `stream`
+ *   (NULL = the context's stream): outputs are valid once the stream has reached this point.
+ *   The first call on each device looks up the array's device address (once, with that device
+ *   current); make that first call before starting any stream capture.
+ *   All calls on a device share the one array, which still holds the previous call's intermediate
+ *   data: the few words that must start at zero are cleared by each call, everything else is
+ *   overwritten before it is read.  Two calls whose GPU work overlaps (different streams, or
+ *   different contexts on the same device) race on the array and give wrong results: run them one
+ *   after the other. */
+#define LWC_STATIC_SCRATCH_BYTES (13u * 1024u * 1024u)
+#define LWC_STATIC_POOL_MAX_ROWS 16384
+#define LWC_STATIC_POOL_MAX_ELEMS 4194304
+int32_t lwc_pool_consensus_static(lwc_ctx *ctx, const lwc_pool_desc *desc, const float *E, const float *V,
+                                  const float *w, float *conf, float *cw, float *agree, int64_t *winner,
+                                  void *stream);
+
 /* NCCL plumbing for the sharded pool: rank 0 creates a 128-byte id, every rank calls lwc_comm_init
  * with it (collective).  NCCL is loaded with dlopen("libnccl.so.2") on first use; 503 if absent. */
 int32_t lwc_comm_unique_id(void *id128);

@@ -26,6 +26,11 @@
 
 #define LWC_VERSION_STRING "lwc_b200 0.1.0 (sm_100a)"
 
+// Working memory of lwc_pool_consensus_static: part of the device image, so no allocation call is ever
+// needed for it.  In host code this name is only a handle for cudaGetSymbolAddress -- it is NOT a
+// device address and must never be handed to a kernel as one.
+static __device__ __align__(256) unsigned char g_static_scratch[LWC_STATIC_SCRATCH_BYTES];
+
 namespace {
 
 std::mutex g_err_mu;
@@ -951,3 +956,110 @@ int32_t lwc_stage_f64(lwc_ctx *ctx, const double *src, size_t n, float *dst) {
 }
 
 } // extern "C"
+
+namespace {
+
+std::mutex g_static_mu;
+unsigned char *g_static_ptr[64] = {nullptr}; // device address of g_static_scratch, per device ordinal
+
+// Resolves (once per device, with that device current) where g_static_scratch lives on ctx's device.
+int static_scratch_address(lwc_ctx *ctx, unsigned char **out) {
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    const int slot = ctx->device & 63;
+    if (!g_static_ptr[slot]) {
+        CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(ctx, LWC_ERR_INTERNAL, "cudaGetSymbolAddress(static scratch) failed on device %d: %s", ctx->device,
+                        cudaGetErrorString(e));
+        g_static_ptr[slot] = static_cast<unsigned char *>(p);
+    }
+    *out = g_static_ptr[slot];
+    return LWC_OK;
+}
+
+__global__ void pool_winner_kernel(const float *__restrict__ scal, const long long *__restrict__ arg,
+                                   long long *__restrict__ winner) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) *winner = scal[0] > 0.f ? arg[0] : -1;
+}
+
+} // namespace
+
+extern "C" int32_t lwc_pool_consensus_static(lwc_ctx *ctx, const lwc_pool_desc *desc, const float *E, const float *V,
+                                             const float *w, float *conf, float *cw, float *agree, int64_t *winner,
+                                             void *stream) {
+    if (!ctx) return LWC_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!desc) return fail(ctx, LWC_ERR_INVALID, "lwc_pool_consensus_static: desc is NULL");
+    const lwc_pool_desc d = *desc;
+    if (d.memory != LWC_MEM_DEVICE)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_pool_consensus_static: every pointer must be device memory (LWC_MEM_DEVICE); "
+                                          "staging host buffers would need an allocation");
+    if (ctx->comm) return fail(ctx, LWC_ERR_INVALID, "lwc_pool_consensus_static: single-GPU only, but a communicator is attached");
+    if (d.N < 1 || d.D < 8 || d.D % 8 != 0 || d.M < 0 || d.M > LWC_MAX_VOTERS)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_pool_consensus_static: invalid shape (N=%lld D=%d M=%d); need N>=1, D%%8==0, 0<=M<=%d",
+                    (long long)d.N, d.D, d.M, LWC_MAX_VOTERS);
+    if (d.N > LWC_STATIC_POOL_MAX_ROWS || d.N * (long long)d.D > LWC_STATIC_POOL_MAX_ELEMS)
+        return fail(ctx, LWC_ERR_INVALID,
+                    "lwc_pool_consensus_static: pool of %lld x %d exceeds the fixed scratch (at most %d rows and %d elements, "
+                    "%u bytes per GPU); use lwc_pool_consensus",
+                    (long long)d.N, d.D, LWC_STATIC_POOL_MAX_ROWS, LWC_STATIC_POOL_MAX_ELEMS, (unsigned)LWC_STATIC_SCRATCH_BYTES);
+    if (d.precision != LWC_PREC_BF16)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_pool_consensus_static: only LWC_PREC_BF16 is implemented for the pool path");
+    if (!E || (d.M > 0 && (!V || !w))) return fail(ctx, LWC_ERR_INVALID, "lwc_pool_consensus_static: NULL input");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    unsigned char *base = nullptr;
+    int rc = static_scratch_address(ctx, &base);
+    if (rc) return rc;
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
+
+    // carve the fixed array (256-byte aligned pieces); sizes follow pool_run's needs
+    const long long n = d.N;
+    const int nblk = (int)((n + lwc::kPoolRedPerBlock - 1) / lwc::kPoolRedPerBlock);
+    const int m1 = d.M > 0 ? d.M : 1;
+    size_t off = 0;
+    auto take = [&off](size_t bytes) {
+        const size_t at = off;
+        off = (off + bytes + 255) & ~(size_t)255;
+        return at;
+    };
+    const size_t o_small = take(1024);                 // scalars first: the only part that must start at zero
+    const size_t o_ehat = take((size_t)n * d.D * 2);
+    const size_t o_t = take((size_t)n * 4);
+    const size_t o_ypart = take((size_t)64 * n * 4);
+    const size_t o_cw = take((size_t)n * 4);
+    const size_t o_conf = take((size_t)n * 4);
+    const size_t o_bsum = take((size_t)2 * (nblk + 16) * 4);
+    const size_t o_barg = take((size_t)(nblk + 16) * 8);
+    const size_t o_bagree = take((size_t)nblk * m1 * 4);
+    const size_t o_agree = take((size_t)m1 * 4);
+    if (off > (size_t)LWC_STATIC_SCRATCH_BYTES)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_pool_consensus_static: needs %zu bytes of scratch, the fixed array has %u", off,
+                    (unsigned)LWC_STATIC_SCRATCH_BYTES);
+    PoolScratch sc;
+    sc.scal = reinterpret_cast<float *>(base + o_small);            // 8 floats
+    sc.arg = reinterpret_cast<long long *>(base + o_small + 512);   // 8 int64
+    sc.ehat_all = reinterpret_cast<__nv_bfloat16 *>(base + o_ehat);
+    sc.t_all = reinterpret_cast<float *>(base + o_t);
+    sc.ypart = reinterpret_cast<float *>(base + o_ypart);
+    sc.cw = reinterpret_cast<float *>(base + o_cw);
+    sc.conf = reinterpret_cast<float *>(base + o_conf);
+    sc.blk_sum = reinterpret_cast<float *>(base + o_bsum);
+    sc.blk_max = sc.blk_sum + nblk + 16;
+    sc.blk_arg = reinterpret_cast<long long *>(base + o_barg);
+    sc.blk_agree = reinterpret_cast<float *>(base + o_bagree);
+    sc.agree = reinterpret_cast<float *>(base + o_agree);
+    // the array still holds the previous call's data: zero the reduction words, the rest is overwritten before use
+    CUDA_TRY(ctx, cudaMemsetAsync(base + o_small, 0, 1024, st));
+    if ((rc = pool_run(ctx, sc, E, V, w, n, d.D, d.M, st))) return rc;
+    if (conf) CUDA_TRY(ctx, cudaMemcpyAsync(conf, sc.conf, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    if (cw) CUDA_TRY(ctx, cudaMemcpyAsync(cw, sc.cw, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    if (agree && d.M > 0) CUDA_TRY(ctx, cudaMemcpyAsync(agree, sc.agree, (size_t)d.M * 4, cudaMemcpyDeviceToDevice, st));
+    if (winner) {
+        pool_winner_kernel<<<1, 32, 0, st>>>(sc.scal, sc.arg, reinterpret_cast<long long *>(winner));
+        CUDA_TRY(ctx, cudaGetLastError());
+        ctx->launches++;
+    }
+    return LWC_OK;
+}

@@ -84,6 +84,8 @@ def load_library():
     L.lwc_vote_from_logprobs.restype = i32
     L.lwc_pool_consensus.argtypes = [vp, ctypes.POINTER(PoolDesc)] + [vp] * 8
     L.lwc_pool_consensus.restype = i32
+    L.lwc_pool_consensus_static.argtypes = [vp, ctypes.POINTER(PoolDesc)] + [vp] * 8
+    L.lwc_pool_consensus_static.restype = i32
     L.lwc_comm_unique_id.argtypes = [vp]
     L.lwc_comm_unique_id.restype = i32
     L.lwc_comm_init.argtypes = [vp, i32, i32, vp]
