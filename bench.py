@@ -328,6 +328,8 @@ def run_b200(args):
 def run_other_workload(args, torch, lwc_b200, synth, local_rank):
     """Kernel-only measurement of another BASELINE.json shape (cfg3/cfg4), single GPU, inputs generated in
     HBM.  Not the driver's bench line: it feeds profiles/ and DESIGN.md."""
+    if args.workload == "pool":
+        return run_pool_workload(args, torch, lwc_b200, local_rank)
     R, N, D, M = synth.CONFIGS[args.workload]
     if args.requests:
         R = args.requests
@@ -381,6 +383,60 @@ def run_other_workload(args, torch, lwc_b200, synth, local_rank):
     return 0
 
 
+def run_pool_workload(args, torch, lwc_b200, local_rank):
+    """Kernel-side measurement of the single-pool path (BASELINE config 5 shape, D = 1024, 16 voters) on one
+    GPU: N rows x N columns all-pairs pass.  Side measurement for profiles/ and DESIGN.md."""
+    import ctypes
+
+    N, D, M = (args.requests or 65536), 1024, 16
+    ctx = lwc_b200.Context(device=local_rank)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    E = torch.randn((N, D), dtype=torch.float32, device="cuda", generator=g)
+    V = torch.rand((M, N), dtype=torch.float32, device="cuda", generator=g) ** 6
+    V /= V.sum(dim=1, keepdim=True)
+    w = torch.rand((M,), dtype=torch.float32, device="cuda", generator=g) + 0.5
+    conf = torch.empty((N,), dtype=torch.float32, device="cuda")
+    cw = torch.empty((N,), dtype=torch.float32, device="cuda")
+    agree = torch.empty((M,), dtype=torch.float32, device="cuda")
+    winner = torch.zeros((1,), dtype=torch.int64, device="cuda")
+    desc = lwc_b200.PoolDesc(N, D, M, lwc_b200.PREC_BF16, lwc_b200.MEM_DEVICE)
+    vp = ctypes.c_void_p
+
+    def step():
+        rc = ctx.lib.lwc_pool_consensus(ctx.handle, ctypes.byref(desc), vp(E.data_ptr()), vp(V.data_ptr()), vp(w.data_ptr()),
+                                        vp(conf.data_ptr()), vp(cw.data_ptr()), vp(agree.data_ptr()), vp(winner.data_ptr()), None)
+        if rc:
+            raise lwc_b200.LwcError(rc, ctx.lib.lwc_last_error_message(ctx.handle).decode())
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    ext = torch.cuda.ExternalStream(ctx.stream())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(ext)
+    for _ in range(args.steps):
+        step()  # blocking: returns after the call's own stream drained
+    e1.record(ext)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    flops = 2.0 * N * N * D
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+        src = "measured (MEASURED_PEAKS.json bf16_tflops, burst)"
+    except Exception:
+        peak, src = 1590.0, "fallback (B200_PROFILING.md)"
+    ach = flops / (ms * 1e-3) / 1e12
+    print(json.dumps({
+        "metric": "pool_all_pairs_per_sec", "value": 1e3 / ms, "unit": "pools/s", "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "dtype": "bf16 operands, f32 accumulate", "data": "synthetic (generated in HBM)",
+        "config": {"workload": f"pool: {N} candidates x {D}-dim, {M} voters, all pairs on one GPU", "kernel": "pool_gemm (tcgen05 kind::f16)"},
+        "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "peak_source": src,
+                     "flops_per_launch": flops},
+        "winner": int(winner.item())}), flush=True)
+    ctx.close()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -388,7 +444,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default=WORKLOAD, choices=["cfg2", "cfg3", "cfg4"],
+    ap.add_argument("--workload", default=WORKLOAD, choices=["cfg2", "cfg3", "cfg4", "pool"],
                     help="cfg2 is the bench line; cfg3/cfg4 are kernel-only side measurements")
     ap.add_argument("--requests", type=int, default=0, help="override R for --workload cfg3/cfg4")
     ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32"])

@@ -255,7 +255,7 @@ inline size_t pool_gemm_smem_bytes() { return 1024 + (size_t)kPoolStages * kPool
 
 // ---------------------------------------------------------------- reductions (fixed order, no atomics)
 constexpr int kPoolRedThreads = 256;
-constexpr int kPoolRedPerBlock = 4096; // rows per block in the reduce/finish kernels
+constexpr int kPoolRedPerBlock = 512;  // rows per block in the reduce/finish kernels (many small blocks: these passes are latency-bound)
 
 // cw[row] = sum_chunks ypart; per-block partial sum and (max, first argmax) of cw
 __global__ void __launch_bounds__(kPoolRedThreads)
