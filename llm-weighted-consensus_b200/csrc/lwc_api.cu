@@ -129,12 +129,13 @@ Plan plan_for(const lwc_batch_desc &d, const void *E) {
         pl.name = pl.np == 16 ? (pl.x3 ? "small16_tf32x3" : "small16_tf32") : (pl.x3 ? "small32_tf32x3" : "small32_tf32");
         return pl;
     }
-    // large pools: the similarity on tcgen05 tensor cores when the caller accepts TF32-grade inputs
-    if (d.N > 32 && aligned && d.D % 32 == 0 && (d.precision == LWC_PREC_TF32 || d.precision == LWC_PREC_BF16)) {
+    // large pools: the similarity on tcgen05 tensor cores -- single-pass TF32 when the caller accepts
+    // TF32-grade inputs, the compensated three-MMA scheme for fp32-grade results
+    if (d.N > 32 && aligned && d.D % 32 == 0) {
         pl.route = ROUTE_TC;
         pl.np = 128;
-        pl.x3 = false;
-        pl.name = "tc128_tf32";
+        pl.x3 = (d.precision == LWC_PREC_FP32 || d.precision == LWC_PREC_TF32X3);
+        pl.name = pl.x3 ? "tc128_tf32x3" : "tc128_tf32";
         return pl;
     }
     pl.route = ROUTE_GENERIC;
@@ -237,18 +238,19 @@ bool make_tensor_map_tc(CUtensorMap *tm, const float *E, int R, int N, int D, in
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+template <bool X3>
 cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
     lwc::TcGeom geo;
-    geo.ko = ctx->tc_ko > 0 ? ctx->tc_ko : 4; // 64 KB boxes x 3 stages streamed fastest (profiles/r1_tma_probe2.txt)
+    geo.ko = ctx->tc_ko > 0 ? ctx->tc_ko : (X3 ? 2 : 4); // 64 KB per stage either way (profiles/r1_tma_probe2.txt)
     const int nslab = p.D / 32;
     if (geo.ko > nslab) geo.ko = nslab;
     geo.stages = lwc::kTcMaxStages;
-    while (geo.stages > 1 && lwc::tc_smem_bytes(geo.ko, geo.stages) > (size_t)ctx->max_smem_optin) --geo.stages;
+    while (geo.stages > 1 && lwc::tc_smem_bytes(geo.ko, geo.stages, X3) > (size_t)ctx->max_smem_optin) --geo.stages;
     if (ctx->tc_stages > 0 && ctx->tc_stages < geo.stages) geo.stages = ctx->tc_stages;
-    if (lwc::tc_smem_bytes(geo.ko, geo.stages) > (size_t)ctx->max_smem_optin) return cudaErrorInvalidConfiguration;
+    if (lwc::tc_smem_bytes(geo.ko, geo.stages, X3) > (size_t)ctx->max_smem_optin) return cudaErrorInvalidConfiguration;
     static bool configured[64] = {false};
     if (!configured[ctx->device & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(lwc::score_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_tc_kernel<X3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              ctx->max_smem_optin);
         if (e != cudaSuccess) return e;
         configured[ctx->device & 63] = true;
@@ -256,7 +258,8 @@ cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) 
     CUtensorMap tm;
     if (!make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, geo.ko)) return cudaErrorInvalidValue;
     const int grid = p.R < ctx->sm_count ? p.R : ctx->sm_count;
-    lwc::score_tc_kernel<<<grid, lwc::kTcThreads, lwc::tc_smem_bytes(geo.ko, geo.stages), st>>>(tm, p, geo);
+    lwc::score_tc_kernel<X3><<<grid, X3 ? lwc::kTcThreadsX3 : lwc::kTcThreads, lwc::tc_smem_bytes(geo.ko, geo.stages, X3), st>>>(
+        tm, p, geo);
     return cudaGetLastError();
 }
 
@@ -314,7 +317,7 @@ int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStr
     // HBM; there the one-CTA-per-request kernel (more warps in flight) measured 83 % vs 80 % of HBM peak.
     const bool stream_route = ctx->small_impl == 0 && !(pl.np == 32 && pl.x3 && !ctx->force_stream);
     if (pl.route == ROUTE_TC) {
-        e = launch_tc(ctx, p, st);
+        e = pl.x3 ? launch_tc<true>(ctx, p, st) : launch_tc<false>(ctx, p, st);
     } else if (pl.route == ROUTE_SMALL && stream_route) {
         if (pl.np == 16)
             e = pl.x3 ? launch_stream<16, true>(ctx, p, st) : launch_stream<16, false>(ctx, p, st);

@@ -20,8 +20,18 @@
 //                    cw_i = (1/n_i) * sum_j u_j S_ij needs only the thread's own row.  Then the
 //                    tally of client.rs:422-449 with block reductions, argmax and rank.
 //
-// Inputs are read by the tensor core as TF32 (the low 13 mantissa bits of each fp32 are ignored):
-// this is the `precision = LWC_PREC_TF32` route with the stated 2e-3 confidence tolerance.
+// X3 = false: inputs are read by the tensor core as TF32 (the low 13 mantissa bits of each fp32 are
+// ignored) -- the `precision = LWC_PREC_TF32` route with the stated 2e-3 confidence tolerance.
+// X3 = true: fp32-grade result.  Four extra "transform" warps (2, 3, 8, 9) turn every landed slab x
+// into its remainder lo = x - trunc_tf32(x) in a twin slab (same swizzled layout, so the transform is
+// purely elementwise), and the issuer runs three MMAs per K step into the SAME accumulator:
+// hi.hi^T + hi.lo^T + lo.hi^T  (hi is what the tensor core sees of x; lo.lo^T < 2^-20 is dropped).
+// The tensor core's fp32 accumulator truncates when it aligns addends: over the 1,152 MMAs of a
+// D = 3072 request the diagonal drifted by ~1e-5 relative (measured), too much for the 1e-5 bar.  So the
+// X3 route accumulates in CHUNKS of kTcChunkStages stages: the two TMEM accumulators alternate per
+// chunk, and the epilogue threads add each finished chunk into fp32 registers (round-to-nearest adds),
+// which bounds every in-TMEM accumulation chain to < 100 MMAs.
+// Three MMAs per step make this route shared-memory-bandwidth bound (operand reads), below HBM speed.
 // Bound: HBM (64 flop/B at N = 128 against a TF32 balance of > 150 flop/B).
 #pragma once
 
@@ -31,9 +41,17 @@
 
 namespace lwc {
 
-constexpr int kTcThreads = 256;
+constexpr int kTcThreads = 256;   // TF32 route: producer, issuer, TMEM allocator, spare, 4 epilogue warps
+constexpr int kTcThreadsX3 = 320; // + warps 8, 9; warps 2, 3, 8, 9 transform
 constexpr int kTcSlabBytes = 128 * 128;  // one [128 rows x 32 fp32] operand slab, SWIZZLE_128B
 constexpr int kTcMaxStages = 8;
+constexpr int kTcChunkStages = 4; // X3: stages per in-TMEM accumulation chunk
+#ifndef LWC_TC_ROUND
+#define LWC_TC_ROUND 0u
+#endif
+// what the tensor core does to an fp32 operand of kind::tf32: 0 = truncate (measured: assuming round-to-
+// nearest, 0x1000, made the compensated route 20x less accurate)
+constexpr uint32_t kTcRound = LWC_TC_ROUND;
 
 struct TcGeom {
     int ko;     // operand slabs (32 columns each) per TMA box / pipeline stage
@@ -97,11 +115,14 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 // named barrier over the 128 epilogue threads only
 __device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-__global__ void __launch_bounds__(kTcThreads, 1)
+template <bool X3>
+__global__ void __launch_bounds__(X3 ? kTcThreadsX3 : kTcThreads, 1)
 score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, const TcGeom geo) {
     extern __shared__ __align__(1024) unsigned char smem_tc[];
     const int KO = geo.ko, S = geo.stages;
-    const int stageb = KO * kTcSlabBytes;
+    const int rawb = KO * kTcSlabBytes;            // bytes the TMA box delivers per stage
+    const int stageb = (X3 ? 2 : 1) * rawb;        // X3: [raw slabs][lo slabs]
+    constexpr int NTW = 4;                         // transform warps (X3 only)
     // dynamic shared memory is only guaranteed 16-byte aligned: SWIZZLE_128B tiles need 1024
     unsigned char *ring = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_tc) + 1023) & ~(uintptr_t)1023);
     float *u_s = reinterpret_cast<float *>(ring + (size_t)S * stageb); // [128] t_i / n_i
@@ -109,9 +130,10 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
     float *part = cf_s + 128;                                         // [16] block-reduction scratch
     int *ipart = reinterpret_cast<int *>(part + 16);                  // [8]
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(ipart + 8);    // [2]
-    uint64_t *bars = reinterpret_cast<uint64_t *>(tmem_slot + 2);     // full[S], empty[S], tfull[2], tempty[2]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(tmem_slot + 2);     // full[S], empty[S], tfull[2], tempty[2], ready[S]
     const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * kTcMaxStages;
     const uint32_t tfull0 = empty0 + 8 * kTcMaxStages, tempty0 = tfull0 + 16;
+    const uint32_t ready0 = tempty0 + 16; // X3: lo slabs of the stage are written and visible to the tensor core
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int N = p.N, D = p.D, M = p.M;
@@ -125,6 +147,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         for (int s = 0; s < S; ++s) {
             mbar_init(full0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, 1);
+            mbar_init(ready0 + 8 * s, NTW);
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(tfull0 + 8 * b, 1);
@@ -151,7 +174,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
             for (int q = 0; q < nreq; ++q)
                 for (int s = 0; s < spr; ++s) {
                     mbar_wait(empty0 + 8 * slot, phase ^ 1u);
-                    mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)stageb); // OOB zero-fill counts too
+                    mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)rawb); // OOB zero-fill counts too
                     tma_load_4d(ring_u32 + slot * stageb, &tmE, 0, 0, s * KO, r_begin + q, full0 + 8 * slot);
                     if (++slot == S) {
                         slot = 0;
@@ -167,22 +190,37 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
             const uint32_t idesc = umma_idesc_tf32(128, 128);
             int slot = 0;
             uint32_t phase = 0;
+            uint32_t tile = 0; // accumulator hand-offs so far: one per request (TF32) or per chunk (X3)
             for (int q = 0; q < nreq; ++q) {
-                const int ab = q & 1;
-                mbar_wait(tempty0 + 8 * ab, (((uint32_t)q >> 1) & 1u) ^ 1u); // accumulator drained by the epilogue
+                uint32_t ab = tile & 1u;
+                mbar_wait(tempty0 + 8 * ab, ((tile >> 1) & 1u) ^ 1u); // accumulator drained by the epilogue
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + (uint32_t)(ab * 128);
+                uint32_t d_tmem = tmem_base + ab * 128u;
                 uint32_t acc = 0;
                 for (int s = 0; s < spr; ++s) {
-                    mbar_wait(full0 + 8 * slot, phase);
+                    if (X3 && s > 0 && s % kTcChunkStages == 0) { // chunk boundary: hand over, switch accumulator
+                        umma_commit(tfull0 + 8 * ab);
+                        ++tile;
+                        ab = tile & 1u;
+                        mbar_wait(tempty0 + 8 * ab, ((tile >> 1) & 1u) ^ 1u);
+                        tc_fence_after();
+                        d_tmem = tmem_base + ab * 128u;
+                        acc = 0;
+                    }
+                    mbar_wait((X3 ? ready0 : full0) + 8 * slot, phase);
                     tc_fence_after();
                     const int nk = min(KO, nslab - s * KO);
                     for (int k = 0; k < nk; ++k) {
                         const uint32_t slab = ring_u32 + slot * stageb + k * kTcSlabBytes;
 #pragma unroll
                         for (int kk = 0; kk < 4; ++kk) { // 4 x K=8 inside the 128-byte swizzle atom
-                            const uint64_t desc = umma_desc_sw128(slab + kk * 32);
-                            umma_tf32(d_tmem, desc, desc, idesc, acc);
+                            const uint64_t hi = umma_desc_sw128(slab + kk * 32);
+                            umma_tf32(d_tmem, hi, hi, idesc, acc);
+                            if (X3) {
+                                const uint64_t lo = umma_desc_sw128(slab + rawb + kk * 32);
+                                umma_tf32(d_tmem, hi, lo, idesc, 1);
+                                umma_tf32(d_tmem, lo, hi, idesc, 1);
+                            }
                             acc = 1;
                         }
                     }
@@ -192,18 +230,51 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                         phase ^= 1u;
                     }
                 }
-                umma_commit(tfull0 + 8 * ab); // accumulator complete
+                umma_commit(tfull0 + 8 * ab); // accumulator (last chunk) complete
+                ++tile;
             }
         }
         __syncwarp();
-    } else if (warp >= 4) {
+    } else if (X3 && (warp == 2 || warp == 3 || warp >= 8)) {
+        // ===================== transform: lo = x - trunc_tf32(x), slab by slab =====================
+        const int tw = warp < 4 ? warp - 2 : warp - 6; // 0..3
+        int slot = 0;
+        uint32_t phase = 0;
+        for (int q = 0; q < nreq; ++q)
+            for (int s = 0; s < spr; ++s) {
+                mbar_wait(full0 + 8 * slot, phase);
+                const float4 *src = reinterpret_cast<const float4 *>(ring + (size_t)slot * stageb);
+                float4 *dst = reinterpret_cast<float4 *>(ring + (size_t)slot * stageb + rawb);
+                const int n16 = rawb >> 4;
+#pragma unroll 4
+                for (int idx = tw * 32 + lane; idx < n16; idx += NTW * 32) {
+                    const float4 x = src[idx];
+                    float4 l;
+                    l.x = x.x - __uint_as_float((__float_as_uint(x.x) + kTcRound) & 0xffffe000u);
+                    l.y = x.y - __uint_as_float((__float_as_uint(x.y) + kTcRound) & 0xffffe000u);
+                    l.z = x.z - __uint_as_float((__float_as_uint(x.z) + kTcRound) & 0xffffe000u);
+                    l.w = x.w - __uint_as_float((__float_as_uint(x.w) + kTcRound) & 0xffffe000u);
+                    dst[idx] = l;
+                }
+                // generic-proxy writes must be visible to the tensor core (async proxy) before it is told
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(ready0 + 8 * slot);
+                if (++slot == S) {
+                    slot = 0;
+                    phase ^= 1u;
+                }
+            }
+    } else if (warp >= 4 && warp < 8) {
         // ===================== epilogue =====================
         const int i = threadIdx.x - 128;   // row of S owned by this thread == TMEM lane
         const int ew = warp - 4;           // TMEM lane quarter this warp may access
         const bool act = i < N;
         const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
+        uint32_t tile = 0;
+        const int nchunk = X3 ? (spr + kTcChunkStages - 1) / kTcChunkStages : 1;
         for (int q = 0; q < nreq; ++q) {
-            const int r = r_begin + q, ab = q & 1;
+            const int r = r_begin + q;
             const float *Vr = p.V + (size_t)r * M * N;
             const float *wr = p.w + (p.w_per_request ? (size_t)r * M : 0);
             // t_i = sum_m w_m V_mi (client.rs:410-415): independent of E, overlaps the MMAs
@@ -215,28 +286,59 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                 if (isnan(wm)) wm = 0.f;
                 if (act) t = fmaf(__ldg(Vr + (size_t)m * N + i), wm, t);
             }
-            mbar_wait(tfull0 + 8 * ab, ((uint32_t)q >> 1) & 1u);
-            tc_fence_after();
-            const uint32_t row_addr = lane_addr + (uint32_t)(ab * 128);
             float v[32];
-            // diagonal: S_ii sits in column chunk `ew` at register index `lane`
-            tmem_ld32(row_addr + (uint32_t)(ew * 32), v);
-            float d = 0.f;
+            float d = 0.f, acc = 0.f, rn = 0.f;
+            if (X3) {
+                // add the chunks' accumulators into registers with ordinary (round-to-nearest) fp32 adds
+                float row[128];
 #pragma unroll
-            for (int e = 0; e < 32; ++e) d = (lane == e) ? v[e] : d;
-            const float rn = (act && d > 0.f) ? 1.0f / sqrtf(d) : 0.f;
-            u_s[i] = t * rn;
-            epi_sync();
-            float acc = 0.f;
+                for (int e = 0; e < 128; ++e) row[e] = 0.f;
+                for (int ch = 0; ch < nchunk; ++ch, ++tile) {
+                    const uint32_t ab = tile & 1u;
+                    mbar_wait(tfull0 + 8 * ab, (tile >> 1) & 1u);
+                    tc_fence_after();
+                    const uint32_t row_addr = lane_addr + ab * 128u;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                tmem_ld32(row_addr + (uint32_t)(c * 32), v);
+                    for (int c = 0; c < 4; ++c) {
+                        tmem_ld32(row_addr + (uint32_t)(c * 32), v);
 #pragma unroll
-                for (int e = 0; e < 32; ++e) acc = fmaf(u_s[c * 32 + e], v[e], acc);
+                        for (int e = 0; e < 32; ++e) row[c * 32 + e] += v[e];
+                    }
+                    tc_fence_before();
+                    mbar_arrive(tempty0 + 8 * ab);
+                }
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) d = (c == ew && lane == e) ? row[c * 32 + e] : d;
+                rn = (act && d > 0.f) ? 1.0f / sqrtf(d) : 0.f;
+                u_s[i] = t * rn;
+                epi_sync();
+#pragma unroll
+                for (int e = 0; e < 128; ++e) acc = fmaf(u_s[e], row[e], acc);
+            } else {
+                const uint32_t ab = tile & 1u;
+                mbar_wait(tfull0 + 8 * ab, (tile >> 1) & 1u);
+                tc_fence_after();
+                const uint32_t row_addr = lane_addr + ab * 128u;
+                // diagonal: S_ii sits in column chunk `ew` at register index `lane`
+                tmem_ld32(row_addr + (uint32_t)(ew * 32), v);
+#pragma unroll
+                for (int e = 0; e < 32; ++e) d = (lane == e) ? v[e] : d;
+                rn = (act && d > 0.f) ? 1.0f / sqrtf(d) : 0.f;
+                u_s[i] = t * rn;
+                epi_sync();
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    tmem_ld32(row_addr + (uint32_t)(c * 32), v);
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) acc = fmaf(u_s[c * 32 + e], v[e], acc);
+                }
+                // accumulator fully read: hand it back to the MMA warp
+                tc_fence_before();
+                mbar_arrive(tempty0 + 8 * ab);
+                ++tile;
             }
-            // accumulator fully read: hand it back to the MMA warp
-            tc_fence_before();
-            mbar_arrive(tempty0 + 8 * ab);
             float c = act ? acc * rn : 0.f;
             // ---- tally (client.rs:422-449) with fixed-order block reductions
             float ws = warp_sum(c);
@@ -306,8 +408,8 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
     }
 }
 
-inline size_t tc_smem_bytes(int ko, int stages) {
-    return 1024 + (size_t)stages * ko * kTcSlabBytes + (128 + 128 + 16 + 8 + 2) * 4 + (2 * kTcMaxStages + 4) * 8 + 64;
+inline size_t tc_smem_bytes(int ko, int stages, bool x3) {
+    return 1024 + (size_t)stages * ko * kTcSlabBytes * (x3 ? 2 : 1) + (128 + 128 + 16 + 8 + 2) * 4 + (3 * kTcMaxStages + 4) * 8 + 64;
 }
 
 } // namespace lwc

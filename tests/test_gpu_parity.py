@@ -265,6 +265,7 @@ def test_cfg4_shape_slice(ctx, lwc, oracle):
     _, N, D, M = synth.CONFIGS["cfg4"]
     R = 24
     E, V, w, kinds = synth.make_batch(R, N, D, M, seed=4)
+    assert ctx.kernel_for(R, N, D, M) == "tc128_tf32x3"  # fp32-grade on tcgen05: three MMAs per K step
     got = ctx.score_batch(E, V, w)
     properties_hold(got, V)
     want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
