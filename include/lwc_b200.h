@@ -212,6 +212,17 @@ int32_t lwc_comm_unique_id(void *id128);
 int32_t lwc_comm_init(lwc_ctx *ctx, int32_t nranks, int32_t rank, const void *id128);
 int32_t lwc_comm_destroy(lwc_ctx *ctx);
 
+/* Optional: fuse the pool path's all-gather INTO the tensor pass.  After lwc_comm_init, every rank
+ * calls lwc_pool_p2p_export for the shard shape it will score (it sizes the context's buffers and
+ * returns two 64-byte CUDA IPC handles), the caller all-gathers the 128-byte records in rank order
+ * (any transport), and every rank calls lwc_pool_p2p_attach with the nranks * 128 bytes.  From then on
+ * lwc_pool_consensus calls with that shape (N % 256 == 0) skip the NCCL all-gather: a gather warp in
+ * every CTA of the tensor kernel pulls the peers' normalised rows over NVLink (peer loads) while the
+ * tensor cores already work on the own shard, and each peer shard is consumed as soon as it has landed.
+ * Only a one-word NCCL all-reduce remains as the cross-rank barrier.  One process per GPU (CUDA IPC). */
+int32_t lwc_pool_p2p_export(lwc_ctx *ctx, int64_t n_own, int32_t D, void *handles_out /* 128 bytes */);
+int32_t lwc_pool_p2p_attach(lwc_ctx *ctx, const void *all_handles /* nranks * 128 bytes */);
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,8 +67,15 @@ struct lwc_ctx {
     int max_smem_optin = 0;
     ncclComm_t comm = nullptr; // attached by lwc_comm_init for the row-sharded pool
     int nranks = 1, rank = 0;
+    // fused peer-to-peer gather of the pool path (lwc_pool_p2p_export / _attach)
+    bool p2p_ready = false;
+    long long p2p_n_own = 0;
+    int p2p_D = 0;
+    void *p2p_mapped[64][2] = {{nullptr}}; // cudaIpcOpenMemHandle results per peer: ehat_all, t_all
+    void *p2p_dev = nullptr;               // device arrays: peer_ehat[nranks], peer_t[nranks], shard_done[nranks]
     void *pool_buf[12] = {nullptr};
     size_t pool_cap[12] = {0};
+    int no_p2p = 0;    // LWC_POOL_NO_P2P=1: keep the NCCL all-gather even when peer mappings are attached
     int tc_ko = 0;     // operand slabs per stage of the tcgen05 kernel (LWC_TC_KO)
     int tc_stages = 0; // its ring depth (LWC_TC_STAGES)
 };
@@ -536,20 +543,31 @@ int pool_run(lwc_ctx *ctx, const PoolScratch &sc, const float *dE, const float *
         CUDA_TRY(ctx, cudaGetLastError());
         ctx->launches++;
     }
-    // 2. the exchange step: all-gather normalised rows and tally vector (in place)
-    if (nranks > 1) {
+    // 2. the exchange step.  Fused route: the tensor pass itself pulls the peers' shards over NVLink, so
+    //    only a stream-ordered cross-rank barrier is needed here (every rank's prep has finished).
+    //    Otherwise: NCCL all-gather of normalised rows and tally vector (in place).
+    const bool fused = nranks > 1 && ctx->p2p_ready && ctx->p2p_n_own == n_own && ctx->p2p_D == D &&
+                       n_own % lwc::kPoolTN == 0 && !ctx->no_p2p;
+    if (fused) {
+        NCCL_TRY(ctx, nc.AllReduce(sc.scal + 4, sc.scal + 4, 1, ncclFloat32, ncclSum, ctx->comm, st));
+        CUDA_TRY(ctx, cudaMemsetAsync(static_cast<char *>(ctx->p2p_dev) + 2 * 64 * sizeof(void *), 0, 64 * sizeof(unsigned), st));
+    } else if (nranks > 1) {
         NCCL_TRY(ctx, nc.AllGather(sc.ehat_all + (size_t)row0 * D, sc.ehat_all, (size_t)n_own * D * 2, ncclUint8, ctx->comm, st));
         NCCL_TRY(ctx, nc.AllGather(sc.t_all + row0, sc.t_all, (size_t)n_own, ncclFloat32, ctx->comm, st));
     }
     // 3. all-pairs pass on tensor cores
     const int nI = (int)((n_own + lwc::kPoolTM - 1) / lwc::kPoolTM);
     const int njb = (int)((n_total + lwc::kPoolTN - 1) / lwc::kPoolTN);
-    int nch = (8 * ctx->sm_count + nI - 1) / nI;
-    if (nch > njb) nch = njb;
-    if (nch > 64) nch = 64;
-    if (nch < 1) nch = 1;
-    const int jbpc = (njb + nch - 1) / nch;
-    nch = (njb + jbpc - 1) / jbpc;
+    // column shards (fused gather: one per rank) x chunks per shard; at most 64 chunks in all
+    const int nshards = fused ? nranks : 1;
+    const int jbs = fused ? (int)(n_own / lwc::kPoolTN) : njb; // 256-column blocks per shard
+    int cps = ((8 * ctx->sm_count + nI - 1) / nI + nshards - 1) / nshards;
+    if (cps > jbs) cps = jbs;
+    if (cps * nshards > 64) cps = 64 / nshards;
+    if (cps < 1) cps = 1;
+    const int jbpc = (jbs + cps - 1) / cps;
+    cps = (jbs + jbpc - 1) / jbpc;
+    const int nch = cps * nshards;
     {
         CUtensorMap tmA, tmB;
         if (!make_tensor_map_bf16_2d(&tmA, sc.ehat_all, n_total, D, lwc::kPoolTM) ||
@@ -565,6 +583,14 @@ int pool_run(lwc_ctx *ctx, const PoolScratch &sc, const float *dE, const float *
         gp.t_all = sc.t_all, gp.ypart = sc.ypart;
         gp.n_own = n_own, gp.n_total = n_total, gp.row0 = row0;
         gp.D = D, gp.nch = nch, gp.jb_per_chunk = jbpc;
+        gp.nshards = nshards, gp.rank = fused ? rank : 0, gp.cps = cps, gp.jb_per_shard = jbs;
+        gp.peer_ehat = nullptr, gp.peer_t = nullptr, gp.ehat_all = sc.ehat_all, gp.t_all_w = sc.t_all, gp.shard_done = nullptr;
+        if (fused) {
+            char *pd = static_cast<char *>(ctx->p2p_dev);
+            gp.peer_ehat = reinterpret_cast<const __nv_bfloat16 *const *>(pd);
+            gp.peer_t = reinterpret_cast<const float *const *>(pd + 64 * sizeof(void *));
+            gp.shard_done = reinterpret_cast<unsigned int *>(pd + 2 * 64 * sizeof(void *));
+        }
         const int nunits = nI * nch;
         const int grid = nunits < ctx->sm_count ? nunits : ctx->sm_count;
         lwc::pool_gemm_kernel<<<grid, lwc::kPoolThreads, lwc::pool_gemm_smem_bytes(), st>>>(tmA, tmB, gp);
@@ -644,6 +670,7 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     if (const char *s = getenv("LWC_STREAM_KC")) ctx->stream_kc = atoi(s);
     if (const char *s = getenv("LWC_STREAM_SLOTS")) ctx->stream_slots = atoi(s);
     if (const char *s = getenv("LWC_STREAM_NF")) ctx->stream_nf = atoi(s);
+    if (const char *s = getenv("LWC_POOL_NO_P2P")) ctx->no_p2p = atoi(s);
     if (const char *s = getenv("LWC_TC_KO")) ctx->tc_ko = atoi(s);
     if (const char *s = getenv("LWC_TC_STAGES")) ctx->tc_stages = atoi(s);
     if (ctx->stream_ncw != 0 && ctx->stream_ncw != 4 && ctx->stream_ncw != 8 && ctx->stream_ncw != 12) ctx->stream_ncw = 0;
@@ -671,6 +698,10 @@ void lwc_ctx_destroy(lwc_ctx *ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+    for (auto &m : ctx->p2p_mapped)
+        for (auto &q : m)
+            if (q) cudaIpcCloseMemHandle(q);
+    if (ctx->p2p_dev) cudaFree(ctx->p2p_dev);
     for (auto &b : ctx->pool_buf)
         if (b) cudaFree(b);
     for (auto &s : ctx->slots) {
@@ -871,6 +902,61 @@ int32_t lwc_comm_destroy(lwc_ctx *ctx) {
         ctx->nranks = 1;
         ctx->rank = 0;
     }
+    return LWC_OK;
+}
+
+int32_t lwc_pool_p2p_export(lwc_ctx *ctx, int64_t n_own, int32_t D, void *handles_out) {
+    if (!ctx || !handles_out) return LWC_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!ctx->comm) return fail(ctx, LWC_ERR_INVALID, "lwc_pool_p2p_export: attach a communicator first (lwc_comm_init)");
+    if (n_own < 1 || D < 8 || D % 8 != 0 || n_own * ctx->nranks > 0x7fffff00LL)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_pool_p2p_export: invalid shape (N=%lld D=%d)", (long long)n_own, D);
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const long long n_total = n_own * ctx->nranks;
+    int rc;
+    // the buffers peers will read from must exist (and stay put) before their handles are handed out
+    if ((rc = pool_ensure(ctx, 0, (size_t)n_total * D * 2))) return rc;
+    if ((rc = pool_ensure(ctx, 1, (size_t)n_total * 4))) return rc;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    cudaIpcMemHandle_t h[2];
+    CUDA_TRY(ctx, cudaIpcGetMemHandle(&h[0], ctx->pool_buf[0]));
+    CUDA_TRY(ctx, cudaIpcGetMemHandle(&h[1], ctx->pool_buf[1]));
+    memcpy(handles_out, h, 128);
+    ctx->p2p_ready = false;
+    ctx->p2p_n_own = n_own;
+    ctx->p2p_D = D;
+    return LWC_OK;
+}
+
+int32_t lwc_pool_p2p_attach(lwc_ctx *ctx, const void *all_handles) {
+    if (!ctx || !all_handles) return LWC_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!ctx->comm || ctx->p2p_n_own == 0)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_pool_p2p_attach: call lwc_comm_init and lwc_pool_p2p_export first");
+    if (ctx->nranks > 64) return fail(ctx, LWC_ERR_INVALID, "lwc_pool_p2p_attach: at most 64 ranks");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const char *hp = static_cast<const char *>(all_handles);
+    void *host_ptrs[2 * 64] = {nullptr};
+    for (int r = 0; r < ctx->nranks; ++r) {
+        for (int k = 0; k < 2; ++k) {
+            void *ptr = ctx->pool_buf[k];
+            if (r != ctx->rank) {
+                if (ctx->p2p_mapped[r][k]) {
+                    cudaIpcCloseMemHandle(ctx->p2p_mapped[r][k]);
+                    ctx->p2p_mapped[r][k] = nullptr;
+                }
+                cudaIpcMemHandle_t h;
+                memcpy(&h, hp + (size_t)r * 128 + k * 64, 64);
+                CUDA_TRY(ctx, cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+                ctx->p2p_mapped[r][k] = ptr;
+            }
+            host_ptrs[k * 64 + r] = ptr;
+        }
+    }
+    if (!ctx->p2p_dev) CUDA_TRY(ctx, cudaMalloc(&ctx->p2p_dev, 2 * 64 * sizeof(void *) + 64 * sizeof(unsigned)));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->p2p_dev, host_ptrs, sizeof host_ptrs, cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->p2p_ready = true;
     return LWC_OK;
 }
 

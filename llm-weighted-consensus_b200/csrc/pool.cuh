@@ -4,7 +4,11 @@
 //
 //   pool_prep_kernel      own rows: n_i = |E_i|, E^_i = E_i / n_i written as bf16 (scratch), and
 //                         t_i = sum_m w_m V_mi (client.rs:410-415).
-//   [NCCL allgather of E^ (bf16) and t over NVLink when nranks > 1 -- the path's one exchange step]
+//   [rows sharded over ranks: the exchange step.  Default: NCCL all-gather of E^ (bf16) and t before the
+//    tensor pass.  With peer mappings attached (lwc_pool_p2p_*): FUSED into pool_gemm_kernel -- a gather
+//    warp in every CTA pulls the peers' shards over NVLink (P2P loads from cudaIpc-mapped memory) into
+//    the local copy while the tensor pass already runs on the own shard's columns, then on each peer
+//    shard as soon as its arrival counter is complete.]
 //   pool_gemm_kernel      y_i = sum_j t_j <E^_i, E^_j> for own rows i, all columns j: 128 x 256 tiles of
 //                         S = E^ E^T on tcgen05 (kind::f16 bf16 operands, fp32 accumulate in TMEM), TMA
 //                         SW128 operand stages; the epilogue folds each S tile into y with the staged
@@ -102,9 +106,44 @@ struct PoolGemmParams {
     long long n_total;    // columns = rows of the whole pool
     long long row0;       // global index of own row 0 (own rows are [row0, row0 + n_own) of E^_all)
     int D;
-    int nch;              // column chunks
+    int nch;              // column chunks in total (= nshards * cps)
     int jb_per_chunk;     // 256-column blocks per chunk
+    // column shards: 1 (single GPU, or gathered beforehand by NCCL) or nranks (fused peer-to-peer gather)
+    int nshards, rank;
+    int cps;              // chunks per shard
+    int jb_per_shard;     // 256-column blocks per shard
+    // fused gather only (nshards > 1):
+    const __nv_bfloat16 *const *peer_ehat; // [nranks] each rank's E^_all base, mapped into this process
+    const float *const *peer_t;            // [nranks] each rank's t_all base
+    __nv_bfloat16 *ehat_all;               // local copy being filled
+    float *t_all_w;
+    unsigned int *shard_done;              // [nranks] CTAs that have finished copying their slice of shard p
 };
+
+// unit u -> (row block I, column shard, chunk id for ypart, 256-column block range).  Units are ordered
+// shard-major starting with the own shard, then chunk-major, so that all CTAs walk the same columns at
+// about the same time (a B stage fetched from HBM by one CTA is an L2 hit for the others) and peer
+// shards are needed in the order rank+1, rank+2, ... (each rank starts pulling from a different peer).
+struct PoolUnit {
+    int I, shard, ychunk, jb0, jb1;
+};
+__device__ __forceinline__ PoolUnit pool_unit(const PoolGemmParams &p, int u, int nI, int njb) {
+    PoolUnit r;
+    const int cidx = u / nI;
+    r.I = u - cidx * nI;
+    const int si = cidx / p.cps, within = cidx - si * p.cps;
+    r.shard = (p.rank + si) % p.nshards;
+    r.ychunk = r.shard * p.cps + within;
+    r.jb0 = r.shard * p.jb_per_shard + within * p.jb_per_chunk;
+    r.jb1 = min(min(njb, (r.shard + 1) * p.jb_per_shard), r.jb0 + p.jb_per_chunk);
+    return r;
+}
+
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int *p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 
 // tmA: bf16 [n_total][D] box {64, 128}; tmB: same tensor, box {64, 256}; both SWIZZLE_128B.
 __global__ void __launch_bounds__(kPoolThreads, 1)
@@ -152,9 +191,18 @@ pool_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const uint32_t ring_u32 = smem_u32(ring);
             int slot = 0;
             uint32_t phase = 0;
+            int shard_seen = p.rank; // shards whose arrival this lane has already confirmed
             for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
-                const int chunk = u / nI, I = u - chunk * nI;
-                const int jb0 = chunk * p.jb_per_chunk, jb1 = min(njb, jb0 + p.jb_per_chunk);
+                const PoolUnit un = pool_unit(p, u, nI, njb);
+                const int I = un.I, jb0 = un.jb0, jb1 = un.jb1;
+                if (p.nshards > 1 && un.shard != shard_seen) {
+                    // fused gather: the shard's rows are being pulled over NVLink by the gather warps of all CTAs
+                    const long long t0 = clock64();
+                    while (ld_acquire_u32(p.shard_done + un.shard) < gridDim.x)
+                        if (clock64() - t0 > 8000000000LL) __trap();
+                    asm volatile("fence.proxy.async;" ::: "memory"); // those generic-proxy stores -> visible to TMA
+                    shard_seen = un.shard;
+                }
                 const int arow = (int)(p.row0 + (long long)I * kPoolTM);
                 for (int jb = jb0; jb < jb1; ++jb)
                     for (int ks = 0; ks < nks; ++ks) {
@@ -178,8 +226,8 @@ pool_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             int slot = 0;
             uint32_t phase = 0, tile = 0;
             for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
-                const int chunk = u / nI;
-                const int jb0 = chunk * p.jb_per_chunk, jb1 = min(njb, jb0 + p.jb_per_chunk);
+                const PoolUnit un = pool_unit(p, u, nI, njb);
+                const int jb0 = un.jb0, jb1 = un.jb1;
                 for (int jb = jb0; jb < jb1; ++jb, ++tile) {
                     const uint32_t ab = tile & 1u;
                     mbar_wait(tempty0 + 8 * ab, ((tile >> 1) & 1u) ^ 1u);
@@ -206,27 +254,59 @@ pool_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
         }
         __syncwarp();
+    } else if (warp == 3) {
+        // ===================== gather (fused collective): pull the peers' shards over NVLink =====================
+        if (p.nshards > 1) {
+            for (int si = 1; si < p.nshards; ++si) {
+                const int src_rank = (p.rank + si) % p.nshards;
+                const size_t row_off = (size_t)src_rank * p.n_own;
+                // tally vector of the shard (CTA-strided)
+                const float *tsrc = p.peer_t[src_rank] + row_off;
+                float *tdst = p.t_all_w + row_off;
+                for (long long k = (long long)blockIdx.x * 32 + lane; k < p.n_own; k += (long long)gridDim.x * 32)
+                    tdst[k] = tsrc[k];
+                // normalised rows: this CTA's slice, 16 bytes per lane and load, 8 loads in flight
+                const uint4 *src = reinterpret_cast<const uint4 *>(p.peer_ehat[src_rank] + row_off * p.D);
+                uint4 *dst = reinterpret_cast<uint4 *>(p.ehat_all + row_off * p.D);
+                const long long n16 = (long long)p.n_own * p.D / 8;
+                const long long b = n16 * blockIdx.x / gridDim.x, e = n16 * (blockIdx.x + 1) / gridDim.x;
+                long long k = b + lane;
+                for (; k + 7 * 32 < e; k += 8 * 32) {
+                    uint4 v[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v[j] = src[k + j * 32];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) dst[k + j * 32] = v[j];
+                }
+                for (; k < e; k += 32) dst[k] = src[k];
+                __threadfence(); // this lane's stores are visible device-wide before the counter moves
+                __syncwarp();
+                if (lane == 0) atomicAdd(p.shard_done + src_rank, 1u);
+            }
+        }
     } else if (warp >= 4) {
         const int i = threadIdx.x - 128;
         const int ew = warp - 4;
         const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
         uint32_t tile = 0;
         for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
-            const int chunk = u / nI, I = u - chunk * nI;
-            const int jb0 = chunk * p.jb_per_chunk, jb1 = min(njb, jb0 + p.jb_per_chunk);
+            const PoolUnit un = pool_unit(p, u, nI, njb);
+            const int chunk = un.ychunk, I = un.I, jb0 = un.jb0, jb1 = un.jb1;
             float y = 0.f;
             for (int jb = jb0; jb < jb1; ++jb, ++tile) {
                 const uint32_t ab = tile & 1u;
                 float *ts = t_s + ab * 256;
-                // stage t_J for this tile (its previous user, tile-2, finished before tempty was released)
+                mbar_wait(tfull0 + 8 * ab, (tile >> 1) & 1u);
+                tc_fence_after();
+                // stage t_J for this tile (its previous user, tile-2, finished before tempty was released).
+                // After the tfull wait: with the fused gather, t of a peer shard exists only once the shard has
+                // arrived, which the producer confirmed before loading this tile.  L2 loads: no stale L1 line.
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     const long long j = (long long)jb * kPoolTN + h * 128 + i;
-                    ts[h * 128 + i] = j < p.n_total ? __ldg(p.t_all + j) : 0.f;
+                    ts[h * 128 + i] = j < p.n_total ? __ldcg(p.t_all + j) : 0.f;
                 }
                 epi_sync();
-                mbar_wait(tfull0 + 8 * ab, (tile >> 1) & 1u);
-                tc_fence_after();
                 const uint32_t row_addr = lane_addr + ab * (uint32_t)kPoolTN;
                 float v[32];
 #pragma unroll 1

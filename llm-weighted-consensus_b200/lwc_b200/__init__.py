@@ -90,6 +90,10 @@ def load_library():
     L.lwc_comm_unique_id.restype = i32
     L.lwc_comm_init.argtypes = [vp, i32, i32, vp]
     L.lwc_comm_init.restype = i32
+    L.lwc_pool_p2p_export.argtypes = [vp, ctypes.c_int64, i32, vp]
+    L.lwc_pool_p2p_export.restype = i32
+    L.lwc_pool_p2p_attach.argtypes = [vp, vp]
+    L.lwc_pool_p2p_attach.restype = i32
     L.lwc_comm_destroy.argtypes = [vp]
     L.lwc_comm_destroy.restype = i32
     L.lwc_stage_f64.argtypes = [vp, vp, ctypes.c_size_t, vp]
@@ -274,6 +278,15 @@ class Context:
     def comm_init(self, nranks, rank, unique_id: bytes):
         buf = ctypes.create_string_buffer(unique_id, 128)
         self._check(self.lib.lwc_comm_init(self.handle, nranks, rank, buf))
+
+    def pool_p2p_export(self, n_own, D) -> bytes:
+        buf = ctypes.create_string_buffer(128)
+        self._check(self.lib.lwc_pool_p2p_export(self.handle, n_own, D, buf))
+        return buf.raw
+
+    def pool_p2p_attach(self, all_handles: bytes):
+        buf = ctypes.create_string_buffer(all_handles, len(all_handles))
+        self._check(self.lib.lwc_pool_p2p_attach(self.handle, buf))
 
     def comm_destroy(self):
         self._check(self.lib.lwc_comm_destroy(self.handle))

@@ -44,6 +44,20 @@ pub struct lwc_batch_desc {
     pub w_per_request: i32,
 }
 
+#[repr(C)]
+#[derive(Clone, Copy, Default)]
+pub struct lwc_pool_desc {
+    pub N: i64,
+    pub D: i32,
+    pub M: i32,
+    pub precision: i32,
+    pub memory: i32,
+}
+
+pub const LWC_STATIC_SCRATCH_BYTES: u32 = 13 * 1024 * 1024;
+pub const LWC_STATIC_POOL_MAX_ROWS: i64 = 16384;
+pub const LWC_STATIC_POOL_MAX_ELEMS: i64 = 4194304;
+
 extern "C" {
     pub fn lwc_ctx_create(cfg: *const lwc_config, out: *mut *mut lwc_ctx) -> i32;
     pub fn lwc_ctx_destroy(ctx: *mut lwc_ctx);
@@ -73,6 +87,19 @@ extern "C" {
     pub fn lwc_launch_count(ctx: *const lwc_ctx) -> u64;
     pub fn lwc_merge_error_codes(codes: *const u16, n_voters: i32) -> i32;
     pub fn lwc_stage_f64(ctx: *mut lwc_ctx, src: *const f64, n: usize, dst: *mut f32) -> i32;
+    pub fn lwc_pool_consensus(
+        ctx: *mut lwc_ctx, desc: *const lwc_pool_desc, E: *const f32, V: *const f32, w: *const f32,
+        conf: *mut f32, cw: *mut f32, agree: *mut f32, winner: *mut i64, stream: *mut c_void,
+    ) -> i32;
+    pub fn lwc_pool_consensus_static(
+        ctx: *mut lwc_ctx, desc: *const lwc_pool_desc, E: *const f32, V: *const f32, w: *const f32,
+        conf: *mut f32, cw: *mut f32, agree: *mut f32, winner: *mut i64, stream: *mut c_void,
+    ) -> i32;
+    pub fn lwc_comm_unique_id(id128: *mut c_void) -> i32;
+    pub fn lwc_comm_init(ctx: *mut lwc_ctx, nranks: i32, rank: i32, id128: *const c_void) -> i32;
+    pub fn lwc_comm_destroy(ctx: *mut lwc_ctx) -> i32;
+    pub fn lwc_pool_p2p_export(ctx: *mut lwc_ctx, n_own: i64, D: i32, handles_out: *mut c_void) -> i32;
+    pub fn lwc_pool_p2p_attach(ctx: *mut lwc_ctx, all_handles: *const c_void) -> i32;
     pub fn lwc_vote_from_logprobs(
         ctx: *mut lwc_ctx,
         n_rows: i32,

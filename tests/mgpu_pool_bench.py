@@ -31,6 +31,12 @@ def main():
     ctx.comm_init(world, rank, ident)
     b, e = shard.pool_rows(n_total, rank, world)
     n = e - b
+    fused = os.environ.get("LWC_POOL_P2P", "0") == "1"
+    if fused:
+        mine = ctx.pool_p2p_export(n, D)
+        handles = [None] * world
+        dist.all_gather_object(handles, mine)
+        ctx.pool_p2p_attach(b"".join(handles))
     g = torch.Generator(device="cuda").manual_seed(100 + rank)
     E = torch.randn((n, D), dtype=torch.float32, device="cuda", generator=g)
     V = torch.rand((M, n), dtype=torch.float32, device="cuda", generator=g) ** 6
@@ -70,7 +76,7 @@ def main():
         flops = 2.0 * n_total * n_total * D
         print(json.dumps({"metric": "pool_all_pairs_per_sec", "value": 1e3 / ms, "unit": "pools/s", "n_gpus": world,
                           "ms_per_step": ms, "steps": steps, "scaling": "strong",
-                          "config": {"workload": f"cfg5: one pool of {n_total} x {D}, {M} voters, rows sharded x{world}, NCCL allgather (bf16 rows)"},
+                          "config": {"workload": f"cfg5: one pool of {n_total} x {D}, {M} voters, rows sharded x{world}, " + ("gather fused into the tensor kernel (P2P over NVLink)" if fused else "NCCL allgather (bf16 rows)")},
                           "aggregate_tflops": flops / (ms * 1e-3) / 1e12, "per_gpu_tflops": flops / (ms * 1e-3) / 1e12 / world,
                           "sum_conf": float(total.item()), "winner_same_on_all_ranks": len(set(winners)) == 1}), flush=True)
     ctx.comm_destroy()

@@ -36,7 +36,19 @@ def main():
     V[2] = np.nan
     w = (rng.integers(50, 201, M) / 100).astype(np.float32)
     Eo, Vo = shard.pool_shard(E, V, rank, world)
+    got_nccl = ctx.pool_consensus(Eo, Vo, w)  # exchange step = NCCL all-gather before the tensor pass
+    # now the fused route: peers' shards are pulled over NVLink inside the tensor kernel
+    mine = ctx.pool_p2p_export(Eo.shape[0], D)
+    handles = [None] * world
+    dist.all_gather_object(handles, mine)
+    ctx.pool_p2p_attach(b"".join(handles))
     got = ctx.pool_consensus(Eo, Vo, w)
+    got2 = ctx.pool_consensus(Eo, Vo, w)      # twice: arrival counters and buffers are reused
+    top_local = float(np.max(np.abs(got_nccl["conf"]))) + 1e-30
+    assert np.max(np.abs(got["conf"] - got_nccl["conf"])) <= 1e-4 * top_local, "fused and NCCL routes disagree"
+    assert got["winner"] == got_nccl["winner"]
+    for k in ("conf", "cw", "agree"):
+        assert np.array_equal(got[k], got2[k], equal_nan=True), k
 
     # every rank must hold identical winner/agree; conf slices reassemble to the whole
     conf_parts = [None] * world

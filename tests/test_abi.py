@@ -75,3 +75,10 @@ def test_product_package_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".hpp", ".rs")):
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "oracle" not in text.lower() or f == "synth.py" and "oracle" not in text.lower(), os.path.join(dirpath, f)
+
+
+def test_rust_sys_crate_declares_every_c_symbol():
+    """rust/lwc-b200-sys cannot be compiled here (no Rust toolchain); at least keep it in step with the header."""
+    rs = open(os.path.join(ROOT, "rust", "lwc-b200-sys", "src", "lib.rs")).read()
+    for name in declared_symbols():
+        assert re.search(r"\bfn %s\b" % name, rs), f"{name} missing from rust/lwc-b200-sys/src/lib.rs"
