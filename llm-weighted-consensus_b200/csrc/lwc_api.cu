@@ -57,6 +57,7 @@ struct lwc_ctx {
     uint64_t launches = 0;
     Slot slots[2];
     int small_kw = 4; // warps per request in the small-pool kernel (LWC_SMALL_KW)
+    int small_kw_set = 0;
     int small_u = 0;  // k-chunks in flight per lane, 0 = per-shape default (LWC_SMALL_U)
     int small_impl = 0;   // 0 = persistent streaming kernel, 1 = one-CTA-per-request kernel (LWC_SMALL_IMPL=direct)
     int force_stream = 0; // LWC_SMALL_IMPL=stream: streaming kernel for every small shape
@@ -218,19 +219,6 @@ EncodeTiledFn encode_tiled_fn() {
     return fn;
 }
 
-// E viewed as a rank-3 fp32 tensor [R][N][D]; one box = [1][rows][cols] (dense in shared memory).
-[[maybe_unused]] bool make_tensor_map_e(CUtensorMap *tm, const float *E, int R, int N, int D, int box_rows, int box_cols) {
-    EncodeTiledFn fn = encode_tiled_fn();
-    if (!fn) return false;
-    cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)N, (cuuint64_t)R};
-    cuuint64_t strides[2] = {(cuuint64_t)D * 4, (cuuint64_t)N * D * 4};
-    cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1};
-    cuuint32_t estr[3] = {1, 1, 1};
-    return fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float *>(E), dims, strides, box, estr,
-              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
-
 // E viewed as a rank-4 fp32 tensor {32 (k_in), N (row), D/32 (k_out), R}: one box {32, 128, ko, 1} lands as
 // ko K-major SWIZZLE_128B operand slabs of [128 rows x 128 B] (score_tc.cuh).
 bool make_tensor_map_tc(CUtensorMap *tm, const float *E, int R, int N, int D, int ko) {
@@ -334,9 +322,9 @@ int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStr
         if (pl.np == 16)
             e = pl.x3 ? launch_small<16, true>(p, st, ctx->small_kw, ctx->small_u)
                       : launch_small<16, false>(p, st, ctx->small_kw, ctx->small_u);
-        else
-            e = pl.x3 ? launch_small<32, true>(p, st, ctx->small_kw, ctx->small_u)
-                      : launch_small<32, false>(p, st, ctx->small_kw, ctx->small_u);
+        else // 32-row pools: 2 warps per request measured best (1.157 vs 1.185 ms at KW=4, cfg3 slice)
+            e = pl.x3 ? launch_small<32, true>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u)
+                      : launch_small<32, false>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u);
     } else {
         if (pl.np == 32)
             e = launch_generic<32>(p, st);
@@ -660,7 +648,10 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     ctx->device = dev;
     ctx->sm_count = prop.multiProcessorCount;
     ctx->chunk_requests = cfg ? cfg->chunk_requests : 0;
-    if (const char *s = getenv("LWC_SMALL_KW")) ctx->small_kw = atoi(s);
+    if (const char *s = getenv("LWC_SMALL_KW")) {
+        ctx->small_kw = atoi(s);
+        ctx->small_kw_set = 1;
+    }
     if (const char *s = getenv("LWC_SMALL_U")) ctx->small_u = atoi(s);
     if (const char *s = getenv("LWC_SMALL_IMPL")) {
         ctx->small_impl = (strcmp(s, "direct") == 0) ? 1 : 0;
