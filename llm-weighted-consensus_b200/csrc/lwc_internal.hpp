@@ -1,0 +1,82 @@
+// lwc_internal.hpp -- shared host-side pieces of the C ABI implementation (not installed).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <mutex>
+#include <string>
+
+#include "../../include/lwc_b200.h"
+
+namespace lwc_host {
+
+struct Slot {
+    void *buf[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t cap[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    cudaEvent_t h2d_done = nullptr; // inputs of this slot are on the device
+    cudaEvent_t all_done = nullptr; // kernel + D2H of this slot finished (slot reusable)
+    bool used = false;
+};
+
+} // namespace lwc_host
+
+struct lwc_ctx {
+    int device = 0;
+    int sm_count = 0;
+    int chunk_requests = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    std::mutex mu;
+    std::string err;
+    uint64_t launches = 0;
+    lwc_host::Slot slots[2];
+    int small_kw = 4; // warps per request in the small-pool kernel (LWC_SMALL_KW)
+    int small_kw_set = 0;
+    int small_u = 0;  // k-chunks in flight per lane, 0 = per-shape default (LWC_SMALL_U)
+    int small_impl = 0;   // 0 = persistent streaming kernel, 1 = one-CTA-per-request kernel (LWC_SMALL_IMPL=direct)
+    int force_stream = 0; // LWC_SMALL_IMPL=stream: streaming kernel for every small shape
+    int stream_ncw = 0;   // consumer warps of the streaming kernel, 0 = per-shape default (LWC_STREAM_NCW)
+    int stream_kc = 0;    // upper bound on columns per stage, 0 = as large as fits (LWC_STREAM_KC)
+    int stream_slots = 0; // ring depth override (LWC_STREAM_SLOTS)
+    int stream_nf = 0;    // finaliser warps, 0 = 1 (LWC_STREAM_NF)
+    int max_smem_optin = 0;
+    ncclComm_t comm = nullptr; // attached by lwc_comm_init for the row-sharded pool
+    int nranks = 1, rank = 0;
+    // fused peer-to-peer gather of the pool path (lwc_pool_p2p_export / _attach)
+    bool p2p_ready = false;
+    long long p2p_n_own = 0;
+    int p2p_D = 0;
+    void *p2p_mapped[64][2] = {{nullptr}}; // cudaIpcOpenMemHandle results per peer: ehat_all, t_all
+    void *p2p_dev = nullptr;               // device arrays: peer_ehat[nranks], peer_t[nranks], shard_done[nranks]
+    void *pool_buf[12] = {nullptr};
+    size_t pool_cap[12] = {0};
+    int no_p2p = 0;    // LWC_POOL_NO_P2P=1: keep the NCCL all-gather even when peer mappings are attached
+    int tc_ko = 0;     // operand slabs per stage of the tcgen05 kernel (LWC_TC_KO)
+    int tc_stages = 0; // its ring depth (LWC_TC_STAGES)
+};
+
+namespace lwc_host {
+
+// Records the failure text (ResponseError.message, src/error.rs:11) and returns `code`.
+int fail(lwc_ctx *ctx, int code, const char *fmt, ...);
+
+#define CUDA_TRY(ctx, expr)                                                                                         \
+    do {                                                                                                            \
+        cudaError_t _e = (expr);                                                                                    \
+        if (_e != cudaSuccess)                                                                                      \
+            return lwc_host::fail((ctx), LWC_ERR_INTERNAL, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                                  __FILE__, __LINE__);                                                              \
+    } while (0)
+
+// cuTensorMapEncodeTiled is a driver entry point; fetched through the runtime so that the library does
+// not link libcuda directly.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn();
+
+} // namespace lwc_host
