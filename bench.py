@@ -192,7 +192,9 @@ def run_b200(args):
     if args.workload != WORKLOAD:
         return run_other_workload(args, torch, lwc_b200, synth, local_rank)
     R, N, D, M = synth.CONFIGS[WORKLOAD]
-    ctx = lwc_b200.Context(device=local_rank)
+    # the device-resident leg keeps its batches in HBM for the whole run, so the context may let
+    # consecutive launches overlap (LWC_CTX_INPUTS_RESIDENT); the host-memory leg ignores the flag
+    ctx = lwc_b200.Context(device=local_rank, flags=0 if args.no_overlap else lwc_b200.CTX_INPUTS_RESIDENT)
     kernel = ctx.kernel_for(R, N, D, M)
 
     # ---- inputs: one pinned host batch (e2e) + three distinct device-resident batches
@@ -302,7 +304,9 @@ def run_b200(args):
         "config": {"workload": f"{WORKLOAD}: {R} requests x {N} candidates x {D}-dim fp32, {M} voters, per GPU",
                    "similarity": "cosine", "precision": "fp32-grade (3xTF32 compensated Gram)",
                    "kernel": kernel, "parallelism": f"request-sharded x{world}, no collectives",
-                   "l2": f"{n_rot} rotating input batches of {hE.nbytes / 1e6:.0f} MB each (> 126 MB L2)"},
+                   "l2": f"{n_rot} rotating input batches of {hE.nbytes / 1e6:.0f} MB each (> 126 MB L2)",
+                   "launches": "serialised" if args.no_overlap else
+                               "programmatic dependent launch: a launch streams its (resident) inputs while the previous one drains"},
         "clocks": sampler.summary(),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "wall_ms_per_step": wall_ms / e2e_steps,
@@ -444,7 +448,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default=WORKLOAD, choices=["cfg2", "cfg3", "cfg4", "pool"],
+    ap.add_argument("--no-overlap", action="store_true", help="do not set LWC_CTX_INPUTS_RESIDENT (launches fully serialised)")
+    ap.add_argument("--workload", default=WORKLOAD, choices=["cfg2", "cfg3", "cfg4", "cfg2x4", "pool"],
                     help="cfg2 is the bench line; cfg3/cfg4 are kernel-only side measurements")
     ap.add_argument("--requests", type=int, default=0, help="override R for --workload cfg3/cfg4")
     ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32"])

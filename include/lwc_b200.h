@@ -56,10 +56,20 @@ extern "C" {
 
 typedef struct lwc_ctx lwc_ctx;
 
+/* lwc_config.flags */
+#define LWC_CTX_INPUTS_RESIDENT 1u /* LWC_MEM_DEVICE calls only: the caller guarantees that E, V and w were
+                                      completely written before the call is issued and are not being written by
+                                      earlier work of the same stream (a batch kept resident in HBM, or uploaded
+                                      and synchronised beforehand).  Consecutive lwc_score_batch launches on one
+                                      stream may then overlap (programmatic dependent launch): the next launch
+                                      streams its inputs while the previous one drains; its result stores still
+                                      wait for the previous launch to finish. */
+
 typedef struct {
     int32_t device;          /* CUDA ordinal this context drives */
     int32_t chunk_requests;  /* host-memory calls are pipelined in chunks of this many requests; 0 = auto */
-    uint64_t reserved[4];
+    uint64_t flags;          /* LWC_CTX_* */
+    uint64_t reserved[3];
 } lwc_config;
 
 enum { LWC_SIM_IDENTITY = 0, /* S = I: the reference tally, client.rs:410-415 */

@@ -220,8 +220,17 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
         configured[ctx->device & 63] = true;
     }
     const int grid = p.R < ctx->sm_count ? p.R : ctx->sm_count;
-    lwc::score_stream_kernel<NT, X3, NCW, NF><<<grid, C::THREADS, C::smem_bytes(geo.ks, geo.stages), st>>>(p, geo);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(C::THREADS);
+    cfg.dynamicSmemBytes = C::smem_bytes(geo.ks, geo.stages);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; // pairs with griddepcontrol.* in the kernel
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, lwc::score_stream_kernel<NT, X3, NCW, NF>, p, geo);
 }
 
 template <int NT, bool X3>
@@ -352,6 +361,7 @@ int score_host(lwc_ctx *ctx, const lwc_batch_desc &d, const Plan &pl, const floa
         p.R = rc_n, p.N = d.N, p.D = d.D, p.M = d.M;
         p.w_per_request = d.w_per_request;
         p.cosine = cosine ? 1 : 0;
+        p.inputs_resident = 0; // staged inputs arrive through the copy stream: keep full stream ordering
         if ((rc = launch_plan(ctx, pl, p, ctx->stream))) return rc;
 
         if (conf)
@@ -411,6 +421,7 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     ctx->device = dev;
     ctx->sm_count = prop.multiProcessorCount;
     ctx->chunk_requests = cfg ? cfg->chunk_requests : 0;
+    ctx->flags = cfg ? cfg->flags : 0;
     if (const char *s = getenv("LWC_SMALL_KW")) {
         ctx->small_kw = atoi(s);
         ctx->small_kw_set = 1;
@@ -555,6 +566,7 @@ int32_t lwc_score_batch(lwc_ctx *ctx, const lwc_batch_desc *desc, const float *E
     p.R = d.R, p.N = d.N, p.D = d.D, p.M = d.M;
     p.w_per_request = d.w_per_request;
     p.cosine = d.similarity == LWC_SIM_COSINE ? 1 : 0;
+    p.inputs_resident = (ctx->flags & LWC_CTX_INPUTS_RESIDENT) ? 1 : 0;
     return launch_plan(ctx, pl, p, stream ? static_cast<cudaStream_t>(stream) : ctx->stream);
 }
 

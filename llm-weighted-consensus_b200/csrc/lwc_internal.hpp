@@ -28,6 +28,7 @@ struct lwc_ctx {
     int device = 0;
     int sm_count = 0;
     int chunk_requests = 0;
+    uint64_t flags = 0; // LWC_CTX_*
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;
     std::mutex mu;

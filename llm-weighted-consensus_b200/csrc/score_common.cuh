@@ -26,7 +26,13 @@ struct ScoreParams {
     int R, N, D, M;
     int w_per_request;
     int cosine;
+    int inputs_resident; // LWC_CTX_INPUTS_RESIDENT: input reads need not wait for the previous grid (PDL)
 };
+
+// Programmatic dependent launch: let the next grid of the stream be scheduled as soon as this one's CTAs
+// retire, and (wait) block until the previous grid has completed and its writes are visible.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait_prior_grid() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 constexpr unsigned kFullMask = 0xffffffffu;
 

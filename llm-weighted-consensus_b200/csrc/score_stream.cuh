@@ -148,6 +148,10 @@ score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    // Back-to-back launches: the next grid may take this SM as soon as this CTA retires.  Unless the
+    // caller vouched for resident inputs, nothing is read before the previous grid has finished.
+    pdl_launch_dependents();
+    if (!p.inputs_resident) pdl_wait_prior_grid();
 
     if (warp == 0) {
         // ===================== producer =====================
@@ -278,6 +282,8 @@ score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
         }
     };
     if (f < nreq) prefetch_votes(r_begin + f);
+    // results may only be stored once the previous grid (which may write the same buffers) is complete
+    if (p.inputs_resident) pdl_wait_prior_grid();
     for (int q = f, k = 0; q < nreq; q += NF, ++k) {
         // wait for the token: the owner of q-1 has drained the park buffer, so the park barrier is
         // exactly in phase q (this warp did not watch the phases in between)

@@ -16,6 +16,7 @@ SIM_IDENTITY, SIM_COSINE = 0, 1
 PREC_FP32, PREC_TF32X3, PREC_TF32, PREC_BF16 = 0, 1, 2, 3
 MEM_HOST, MEM_DEVICE = 0, 1
 MAX_CHOICES, MAX_VOTERS = 128, 128
+CTX_INPUTS_RESIDENT = 1
 
 
 class LwcError(RuntimeError):
@@ -38,7 +39,8 @@ class PoolDesc(ctypes.Structure):
 
 
 class Config(ctypes.Structure):
-    _fields_ = [("device", ctypes.c_int32), ("chunk_requests", ctypes.c_int32), ("reserved", ctypes.c_uint64 * 4)]
+    _fields_ = [("device", ctypes.c_int32), ("chunk_requests", ctypes.c_int32), ("flags", ctypes.c_uint64),
+                ("reserved", ctypes.c_uint64 * 3)]
 
 
 _lib = None
@@ -174,9 +176,9 @@ class DeviceBuffer:
 
 
 class Context:
-    def __init__(self, device=0, chunk_requests=0):
+    def __init__(self, device=0, chunk_requests=0, flags=0):
         self.lib = load_library()
-        cfg = Config(device=device, chunk_requests=chunk_requests)
+        cfg = Config(device=device, chunk_requests=chunk_requests, flags=flags)
         h = ctypes.c_void_p()
         rc = self.lib.lwc_ctx_create(ctypes.byref(cfg), ctypes.byref(h))
         if rc:

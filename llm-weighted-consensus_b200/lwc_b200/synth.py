@@ -16,6 +16,7 @@ CONFIGS = {
     "cfg2": (4096, 16, 1536, 4),
     "cfg3": (65536, 32, 3072, 4),
     "cfg4": (8192, 128, 3072, 16),
+    "cfg2x4": (16384, 16, 1536, 4),  # cfg2's shape at 4x the batch: separates per-launch overhead from streaming rate
 }
 
 

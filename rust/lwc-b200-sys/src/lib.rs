@@ -17,6 +17,7 @@ pub const LWC_PREC_TF32: i32 = 2;
 pub const LWC_PREC_BF16: i32 = 3;
 pub const LWC_MEM_HOST: i32 = 0;
 pub const LWC_MEM_DEVICE: i32 = 1;
+pub const LWC_CTX_INPUTS_RESIDENT: u64 = 1;
 
 #[repr(C)]
 pub struct lwc_ctx {
@@ -28,7 +29,8 @@ pub struct lwc_ctx {
 pub struct lwc_config {
     pub device: i32,
     pub chunk_requests: i32,
-    pub reserved: [u64; 4],
+    pub flags: u64,
+    pub reserved: [u64; 3],
 }
 
 #[repr(C)]

@@ -361,3 +361,36 @@ def test_large_pool_exact_tie_and_order_invariance(ctx, lwc):
     again = ctx.score_batch_device(E[perm], V[perm], w[perm], precision=lwc.PREC_TF32)
     for k in got:
         assert np.array_equal(again[k], got[k][perm], equal_nan=True), k
+
+
+def test_overlapped_launches_with_resident_inputs(lwc, oracle):
+    """LWC_CTX_INPUTS_RESIDENT lets back-to-back launches overlap (programmatic dependent launch).  The
+    result stores of a launch must still land after the previous launch's: alternate two different
+    batches into the SAME output buffers many times and check that the last writer wins every time."""
+    import ctypes
+
+    from lwc_b200 import synth
+
+    R, N, D, M = 1500, 16, 1536, 4
+    batches = [synth.make_batch(R, N, D, M, seed=s, edge_cases=False)[:3] for s in (31, 32)]
+    with lwc.Context(device=0, flags=lwc.CTX_INPUTS_RESIDENT) as ctx, lwc.Context(device=0) as plain:
+        want = [plain.score_batch_device(E, V, w) for E, V, w in batches]
+        dev = []
+        for E, V, w in batches:
+            dev.append((lwc.DeviceBuffer(ctx, E.nbytes).upload(E), lwc.DeviceBuffer(ctx, V.nbytes).upload(V),
+                        lwc.DeviceBuffer(ctx, w.nbytes).upload(w)))
+        outs = [lwc.DeviceBuffer(ctx, 4 * R * N), lwc.DeviceBuffer(ctx, 4 * R * N), lwc.DeviceBuffer(ctx, 4 * R * M),
+                lwc.DeviceBuffer(ctx, 4 * R), lwc.DeviceBuffer(ctx, 4 * R * N)]
+        desc = lwc.BatchDesc(R, N, D, M, lwc.SIM_COSINE, lwc.PREC_FP32, lwc.MEM_DEVICE, 1)
+        for trial in range(6):
+            n_launch = 7 + trial  # odd and even counts: either batch may be the last writer
+            for k in range(n_launch):
+                dE, dV, dw = dev[k & 1]
+                ctx.score_raw(desc, dE.ptr, dV.ptr, dw.ptr, *[o.ptr for o in outs])
+            ctx.synchronize()
+            last = want[(n_launch - 1) & 1]
+            assert np.array_equal(outs[0].download((R, N), np.float32), last["conf"])
+            assert np.array_equal(outs[3].download((R,), np.int32), last["winner"])
+            assert np.array_equal(outs[4].download((R, N), np.int32), last["rank"])
+        for b in outs + [x for t in dev for x in t]:
+            b.free()
