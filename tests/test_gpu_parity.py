@@ -394,3 +394,40 @@ def test_overlapped_launches_with_resident_inputs(lwc, oracle):
             assert np.array_equal(outs[4].download((R, N), np.int32), last["rank"])
         for b in outs + [x for t in dev for x in t]:
             b.free()
+
+
+# ------------------------------------------------------------------ shape extremes
+
+EXTREMES = [
+    # (R, N, D, M, precision-name)
+    (1, 16, 1536, 4, "fp32"),      # a single request: one CTA of the persistent kernel
+    (1, 128, 3072, 16, "fp32"),    # a single large pool on tcgen05 (fp32-grade)
+    (1, 128, 3072, 16, "tf32"),
+    (3, 16, 16384, 2, "fp32"),     # very long rows: 22 streaming stages per request
+    (2, 32, 8192, 3, "fp32"),
+    (150, 1, 64, 2, "fp32"),       # degenerate pool of one candidate
+    (149, 2, 4, 1, "fp32"),        # one more request than SMs, smallest aligned D
+    (5, 128, 32, 4, "tf32"),       # one operand slab per request
+    (5, 40, 64, 4, "fp32"),
+    (300, 16, 1536, 0, "fp32"),    # no voters: every confidence 0, winner -1
+]
+
+
+@pytest.mark.parametrize("case", EXTREMES, ids=lambda c: "R%d_N%d_D%d_M%d_%s" % c)
+def test_shape_extremes(ctx, lwc, oracle, case):
+    from lwc_b200 import synth
+
+    R, N, D, M, prec = case
+    E, V, w, _ = synth.make_batch(R, N, D, M, seed=R * 131 + N + D, edge_cases=False)
+    p = lwc.PREC_FP32 if prec == "fp32" else lwc.PREC_TF32
+    got = ctx.score_batch_device(E, V, w, precision=p)
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    if prec == "fp32":
+        compare(got, want, V)
+    else:
+        compare(got, want, V, rtol=TF32_RTOL, atol=1e-5, gap=5e-3, min_agreement=0.95, atol_of_max=TF32_RTOL)
+    if M == 0:
+        assert np.all(got["winner"] == -1) and np.all(got["conf"] == 0)
+    if N == 1 and M > 0:
+        scored = got["winner"] >= 0
+        assert np.all(got["conf"][scored, 0] == 1.0)
