@@ -190,7 +190,7 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     if args.workload != WORKLOAD:
-        return run_other_workload(args, torch, lwc_b200, synth, local_rank)
+        return run_other_workload(args, torch, lwc_b200, synth, local_rank, rank, world, dist)
     R, N, D, M = synth.CONFIGS[WORKLOAD]
     # the device-resident leg keeps its batches in HBM for the whole run, so the context may let
     # consecutive launches overlap (LWC_CTX_INPUTS_RESIDENT); the host-memory leg ignores the flag
@@ -329,14 +329,19 @@ def run_b200(args):
     return 0
 
 
-def run_other_workload(args, torch, lwc_b200, synth, local_rank):
-    """Kernel-only measurement of another BASELINE.json shape (cfg3/cfg4), single GPU, inputs generated in
-    HBM.  Not the driver's bench line: it feeds profiles/ and DESIGN.md."""
+def run_other_workload(args, torch, lwc_b200, synth, local_rank, rank=0, world=1, dist=None):
+    """Kernel-only measurement of another BASELINE.json shape (cfg3/cfg4), inputs generated in HBM.  Under
+    torchrun the R requests of the config are sharded by request over the ranks (strong scaling, no
+    collective; BASELINE config 3 is quoted that way).  Not the driver's bench line: it feeds profiles/."""
+    from lwc_b200 import shard
+
     if args.workload == "pool":
         return run_pool_workload(args, torch, lwc_b200, local_rank)
-    R, N, D, M = synth.CONFIGS[args.workload]
+    R_total, N, D, M = synth.CONFIGS[args.workload]
     if args.requests:
-        R = args.requests
+        R_total = args.requests
+    b, e = shard.request_block(R_total, rank, world)
+    R = e - b
     prec = {"fp32": lwc_b200.PREC_FP32, "tf32": lwc_b200.PREC_TF32}[args.precision]
     ctx = lwc_b200.Context(device=local_rank)
     kernel = ctx.kernel_for(R, N, D, M, precision=prec)
@@ -362,6 +367,8 @@ def run_other_workload(args, torch, lwc_b200, synth, local_rank):
 
     for i in range(args.warmup):
         step(i)
+    if dist is not None:
+        dist.barrier()
     torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with torch.cuda.stream(stream):
@@ -370,20 +377,29 @@ def run_other_workload(args, torch, lwc_b200, synth, local_rank):
             step(i)
         ev1.record(stream)
     torch.cuda.synchronize()
-    ms = ev0.elapsed_time(ev1) / args.steps
+    if dist is not None:
+        dist.barrier()
+    ms = shard.max_over_ranks(dist, ev0.elapsed_time(ev1) / args.steps, device="cuda")
     peak, peak_src = load_peaks()
-    nbytes = R * synth.algorithmic_bytes_per_request(N, D, M)
+    nbytes = R * synth.algorithmic_bytes_per_request(N, D, M)  # per GPU: the roofline is a per-GPU statement
     flops = R * synth.algorithmic_flops_per_request(N, D, M)
     achieved = nbytes / (ms * 1e-3) / 1e9
-    print(json.dumps({
-        "metric": METRIC, "value": R / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms, "dtype": "f32", "data": "synthetic (generated in HBM)",
-        "config": {"workload": f"{args.workload}: {R} requests x {N} candidates x {D}-dim fp32, {M} voters",
-                   "kernel": kernel, "precision": args.precision, "l2": f"{n_rot} rotating batches of {dE[0].numel() * 4 / 1e9:.2f} GB"},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "peak_source": peak_src, "bytes_per_launch": nbytes, "algorithmic_tflops": flops / (ms * 1e-3) / 1e12},
-        "gpu_launches": args.steps}), flush=True)
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": R_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "scaling": "strong", "dtype": "f32",
+            "data": "synthetic (generated in HBM)",
+            "config": {"workload": f"{args.workload}: {R_total} requests x {N} candidates x {D}-dim fp32, {M} voters"
+                                   + (f", sharded by request x{world} ({R} per GPU), no collective" if world > 1 else ""),
+                       "kernel": kernel, "precision": args.precision,
+                       "l2": f"{n_rot} rotating batches of {dE[0].numel() * 4 / 1e9:.2f} GB per GPU"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "peak_source": peak_src, "bytes_per_launch": nbytes, "scope": "per GPU",
+                         "algorithmic_tflops": flops / (ms * 1e-3) / 1e12},
+            "gpu_launches": args.steps}), flush=True)
     ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
     return 0
 
 

@@ -256,9 +256,12 @@ class Batcher {
     void score(std::vector<std::unique_ptr<Job>> &batch) {
         const int R = (int)batch.size(), N = batch[0]->N, D = batch[0]->D, M = batch[0]->M;
         try {
-            Pinned<float> E(ctx_, (size_t)R * N * std::max(D, 1)), V(ctx_, (size_t)R * std::max(M, 1) * N), w(ctx_, (size_t)R * std::max(M, 1));
-            Pinned<float> conf(ctx_, (size_t)R * N), cw(ctx_, (size_t)R * N), agree(ctx_, (size_t)R * std::max(M, 1));
-            Pinned<int32_t> winner(ctx_, R), rank(ctx_, (size_t)R * N);
+            // pinned staging is kept across batches and only ever grows: cudaHostAlloc costs milliseconds
+            Arena E(arena_[0], ctx_, (size_t)R * N * std::max(D, 1)), V(arena_[1], ctx_, (size_t)R * std::max(M, 1) * N),
+                w(arena_[2], ctx_, (size_t)R * std::max(M, 1));
+            Arena conf(arena_[3], ctx_, (size_t)R * N), cw(arena_[4], ctx_, (size_t)R * N),
+                agree(arena_[5], ctx_, (size_t)R * std::max(M, 1));
+            ArenaI winner(arena_[6], ctx_, (size_t)R), rank(arena_[7], ctx_, (size_t)R * N);
             for (int r = 0; r < R; ++r) {
                 if (D) std::memcpy(E.data() + (size_t)r * N * D, batch[r]->E.data(), sizeof(float) * N * D);
                 if (M) std::memcpy(V.data() + (size_t)r * M * N, batch[r]->V.data(), sizeof(float) * M * N);
@@ -297,8 +300,28 @@ class Batcher {
         }
     }
 
+    // view of a grow-only pinned buffer (one per role; touched by the worker thread only)
+    template <class T>
+    struct ArenaT {
+        ArenaT(std::unique_ptr<Pinned<T>> &slot, const Context &c, size_t n) {
+            if (!slot || slot->size() < n) slot = std::make_unique<Pinned<T>>(c, n + n / 4 + 64);
+            p = slot->data();
+        }
+        T *data() { return p; }
+        T *p;
+    };
+    struct Arena : ArenaT<float> {
+        Arena(std::unique_ptr<Pinned<float>> &s, const Context &c, size_t n) : ArenaT<float>(s, c, n) {}
+    };
+    struct ArenaI {
+        ArenaI(std::unique_ptr<Pinned<float>> &s, const Context &c, size_t n) : a(s, c, n) {}
+        int32_t *data() { return reinterpret_cast<int32_t *>(a.data()); }
+        ArenaT<float> a;
+    };
+
     Context ctx_;
     Options opt_;
+    std::unique_ptr<Pinned<float>> arena_[8];
     std::mutex mu_;
     std::condition_variable cv_;
     std::map<Key, std::deque<std::unique_ptr<Job>>> queue_;
