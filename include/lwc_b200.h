@@ -233,6 +233,25 @@ int32_t lwc_comm_destroy(lwc_ctx *ctx);
 int32_t lwc_pool_p2p_export(lwc_ctx *ctx, int64_t n_own, int32_t D, void *handles_out /* 128 bytes */);
 int32_t lwc_pool_p2p_attach(lwc_ctx *ctx, const void *all_handles /* nranks * 128 bytes */);
 
+/* Training-table weights.  Fills the slot the reference leaves `unimplemented!()`:
+ * weight::Fetcher for WeightType::TrainingTable (src/score/completions/weight.rs:99-117), configured by
+ * `WeightTrainingTable { embeddings, top }` (src/score/model/mod.rs:278-306) and the per-LLM
+ * `base_weight / min_weight / max_weight` (src/score/llm/mod.rs:663-688).  The reference holds no
+ * arithmetic for it, so the policy is BUILD-DEFINED and its parity is unpinned.
+ *
+ * lwc_table_load: copies a table of `rows` past prompts to the GPU and keeps it resident in the
+ *   context: T [rows][D] prompt embeddings, Q [rows][M] each LLM's recorded quality on that prompt
+ *   (>= 0; e.g. the confidence it gave the winning choice).  Replaces a previously loaded table.
+ * lwc_table_weights: for each of n_prompts new prompt embeddings q [n_prompts][D] (host memory), finds
+ *   the `top` most cosine-similar table rows (ties -> lowest row) and writes
+ *     weights[p][m] = clamp(base[m] * rho_m / mean_m'(rho_m'), minw[m], maxw[m]),
+ *     rho_m = sum_k max(sim_k, 0) Q[idx_k][m] / sum_k max(sim_k, 0);   base[m] when no neighbour has sim > 0.
+ *   400 unless 0 < minw <= base <= maxw for every LLM (the reference's validate()) and 1 <= top <= 64.
+ *   top_idx / top_sim ([n_prompts][top], -1 / 0 past the table's size) may be NULL.  Blocking. */
+int32_t lwc_table_load(lwc_ctx *ctx, const float *T, const float *Q, int64_t rows, int32_t D, int32_t M);
+int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32_t top, const float *base,
+                          const float *minw, const float *maxw, float *weights, int32_t *top_idx, float *top_sim);
+
 #ifdef __cplusplus
 }
 #endif

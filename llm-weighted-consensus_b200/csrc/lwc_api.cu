@@ -468,6 +468,8 @@ void lwc_ctx_destroy(lwc_ctx *ctx) {
         for (auto &q : m)
             if (q) cudaIpcCloseMemHandle(q);
     if (ctx->p2p_dev) cudaFree(ctx->p2p_dev);
+    for (auto &b : ctx->table_buf)
+        if (b) cudaFree(b);
     for (auto &b : ctx->pool_buf)
         if (b) cudaFree(b);
     for (auto &s : ctx->slots) {

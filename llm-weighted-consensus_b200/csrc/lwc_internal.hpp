@@ -56,6 +56,11 @@ struct lwc_ctx {
     void *pool_buf[12] = {nullptr};
     size_t pool_cap[12] = {0};
     int no_p2p = 0;    // LWC_POOL_NO_P2P=1: keep the NCCL all-gather even when peer mappings are attached
+    // resident training table (lwc_table_load): embeddings, inverse norms, per-LLM scores, scratch
+    void *table_buf[5] = {nullptr};
+    size_t table_cap[5] = {0};
+    long long table_rows = 0;
+    int table_D = 0, table_M = 0;
     int tc_ko = 0;     // operand slabs per stage of the tcgen05 kernel (LWC_TC_KO)
     int tc_stages = 0; // its ring depth (LWC_TC_STAGES)
 };

@@ -1,0 +1,119 @@
+// lwc_table_api.cu -- C ABI of the training-table weight lookup (BUILD-DEFINED, see table.cuh).
+#include <cstring>
+
+#include "lwc_internal.hpp"
+#include "table.cuh"
+
+using lwc_host::fail;
+
+namespace {
+
+int table_ensure(lwc_ctx *ctx, int which, size_t bytes) {
+    if (bytes <= ctx->table_cap[which]) return LWC_OK;
+    if (ctx->table_buf[which]) CUDA_TRY(ctx, cudaFree(ctx->table_buf[which]));
+    ctx->table_buf[which] = nullptr;
+    ctx->table_cap[which] = 0;
+    CUDA_TRY(ctx, cudaMalloc(&ctx->table_buf[which], bytes + 256));
+    ctx->table_cap[which] = bytes + 256;
+    return LWC_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int32_t lwc_table_load(lwc_ctx *ctx, const float *T, const float *Q, int64_t rows, int32_t D, int32_t M) {
+    if (!ctx) return LWC_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!T || !Q || rows < 1 || rows > 0x7fffffffLL || D < 1 || M < 1 || M > LWC_MAX_VOTERS)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_table_load: invalid table (rows=%lld D=%d M=%d)", (long long)rows, D, M);
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    int rc;
+    if ((rc = table_ensure(ctx, 0, (size_t)rows * D * 4))) return rc;
+    if ((rc = table_ensure(ctx, 1, (size_t)rows * 4))) return rc;
+    if ((rc = table_ensure(ctx, 2, (size_t)rows * M * 4))) return rc;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->table_buf[0], T, (size_t)rows * D * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->table_buf[2], Q, (size_t)rows * M * 4, cudaMemcpyHostToDevice, ctx->stream));
+    const int warps = 8;
+    lwc::table_norm_kernel<<<(unsigned)((rows + warps - 1) / warps), warps * 32, 0, ctx->stream>>>(
+        static_cast<const float *>(ctx->table_buf[0]), static_cast<float *>(ctx->table_buf[1]), rows, D);
+    CUDA_TRY(ctx, cudaGetLastError());
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->table_rows = rows;
+    ctx->table_D = D;
+    ctx->table_M = M;
+    return LWC_OK;
+}
+
+int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32_t top, const float *base,
+                          const float *minw, const float *maxw, float *weights, int32_t *top_idx, float *top_sim) {
+    if (!ctx) return LWC_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (ctx->table_rows == 0) return fail(ctx, LWC_ERR_INVALID, "lwc_table_weights: no table loaded (lwc_table_load)");
+    // `top` >= 1 as WeightTrainingTable::validate demands (src/score/model/mod.rs:292-297)
+    if (!q || !base || !minw || !maxw || !weights || n_prompts < 0 || top < 1 || top > lwc::kTableMaxTop)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_table_weights: invalid argument (prompts=%d top=%d, top must be 1..%d)",
+                    n_prompts, top, lwc::kTableMaxTop);
+    const int M = ctx->table_M, D = ctx->table_D;
+    const long long Tn = ctx->table_rows;
+    for (int m = 0; m < M; ++m) // WeightTrainingTable::validate, src/score/llm/mod.rs:671-687
+        if (!(minw[m] > 0.f) || !(base[m] >= minw[m]) || !(base[m] <= maxw[m]))
+            return fail(ctx, LWC_ERR_INVALID, "lwc_table_weights: LLM %d needs 0 < min <= base <= max (got %g, %g, %g)", m,
+                        minw[m], base[m], maxw[m]);
+    if (n_prompts == 0) return LWC_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int QB = lwc::kTableQB;
+    int rc;
+    // scratch: [3] scores [QB][Tn] | per-chunk candidates (value, row) [QB][chunks][top]; [4] q | idx | sim | limits | weights for one pass
+    const long long chunks = (Tn + lwc::kTopkChunk - 1) / lwc::kTopkChunk;
+    const size_t o_cv = ((size_t)QB * Tn * 4 + 255) & ~(size_t)255, cand_bytes = (size_t)QB * chunks * top * 4;
+    if ((rc = table_ensure(ctx, 3, o_cv + 2 * cand_bytes))) return rc;
+    char *s3 = static_cast<char *>(ctx->table_buf[3]);
+    const size_t o_q = 0, o_idx = (size_t)QB * D * 4, o_sim = o_idx + (size_t)QB * top * 4, o_lim = o_sim + (size_t)QB * top * 4,
+                 o_w = o_lim + (size_t)3 * M * 4, total = o_w + (size_t)QB * M * 4;
+    if ((rc = table_ensure(ctx, 4, total))) return rc;
+    char *sb = static_cast<char *>(ctx->table_buf[4]);
+    CUDA_TRY(ctx, cudaMemcpyAsync(sb + o_lim, base, (size_t)M * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(sb + o_lim + (size_t)M * 4, minw, (size_t)M * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(sb + o_lim + (size_t)2 * M * 4, maxw, (size_t)M * 4, cudaMemcpyHostToDevice, st));
+    const size_t smem = ((size_t)QB * D + QB) * 4;
+    static bool configured[64] = {false};
+    if (smem > 48 * 1024 && !configured[ctx->device & 63]) {
+        CUDA_TRY(ctx, cudaFuncSetAttribute(lwc::table_scores_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           ctx->max_smem_optin));
+        configured[ctx->device & 63] = true;
+    }
+    if (smem > (size_t)ctx->max_smem_optin)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_table_weights: D=%d too large for the prompt tile in shared memory", D);
+    for (int b0 = 0; b0 < n_prompts; b0 += QB) {
+        const int nq = n_prompts - b0 < QB ? n_prompts - b0 : QB;
+        CUDA_TRY(ctx, cudaMemcpyAsync(sb + o_q, q + (size_t)b0 * D, (size_t)nq * D * 4, cudaMemcpyHostToDevice, st));
+        long long blocks = (Tn + 8 * lwc::kTableRows - 1) / (8 * lwc::kTableRows);
+        if (blocks > 8LL * ctx->sm_count) blocks = 8LL * ctx->sm_count;
+        lwc::table_scores_kernel<<<(unsigned)blocks, 256, ((size_t)nq * D + nq) * 4, st>>>(
+            static_cast<const float *>(ctx->table_buf[0]), static_cast<const float *>(ctx->table_buf[1]),
+            reinterpret_cast<const float *>(sb + o_q), static_cast<float *>(ctx->table_buf[3]), Tn, D, nq);
+        lwc::table_topk_part_kernel<<<dim3((unsigned)chunks, nq), 1024, 0, st>>>(
+            reinterpret_cast<const float *>(s3), Tn, top, reinterpret_cast<float *>(s3 + o_cv),
+            reinterpret_cast<int32_t *>(s3 + o_cv + cand_bytes));
+        lwc::table_topk_merge_kernel<<<nq, 1024, 0, st>>>(reinterpret_cast<float *>(s3 + o_cv),
+                                                          reinterpret_cast<const int32_t *>(s3 + o_cv + cand_bytes), chunks * top, top,
+                                                          reinterpret_cast<int32_t *>(sb + o_idx), reinterpret_cast<float *>(sb + o_sim));
+        lwc::table_weights_kernel<<<(nq + 3) / 4, 128, 0, st>>>(
+            reinterpret_cast<const int32_t *>(sb + o_idx), reinterpret_cast<const float *>(sb + o_sim),
+            static_cast<const float *>(ctx->table_buf[2]), reinterpret_cast<const float *>(sb + o_lim),
+            reinterpret_cast<const float *>(sb + o_lim + (size_t)M * 4), reinterpret_cast<const float *>(sb + o_lim + (size_t)2 * M * 4),
+            reinterpret_cast<float *>(sb + o_w), nq, top, M);
+        CUDA_TRY(ctx, cudaGetLastError());
+        ctx->launches += 4;
+        CUDA_TRY(ctx, cudaMemcpyAsync(weights + (size_t)b0 * M, sb + o_w, (size_t)nq * M * 4, cudaMemcpyDeviceToHost, st));
+        if (top_idx) CUDA_TRY(ctx, cudaMemcpyAsync(top_idx + (size_t)b0 * top, sb + o_idx, (size_t)nq * top * 4, cudaMemcpyDeviceToHost, st));
+        if (top_sim) CUDA_TRY(ctx, cudaMemcpyAsync(top_sim + (size_t)b0 * top, sb + o_sim, (size_t)nq * top * 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(ctx, cudaStreamSynchronize(st)); // the pass's scratch is reused by the next one
+    }
+    return LWC_OK;
+}
+
+} // extern "C"

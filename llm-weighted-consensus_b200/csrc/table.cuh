@@ -1,0 +1,249 @@
+// table.cuh -- training-table weight lookup: the slot the reference ships as
+// `unimplemented!()` (src/score/completions/weight.rs:99-117; config `WeightTrainingTable { embeddings, top }`,
+// src/score/model/mod.rs:278-306; per-LLM `base_weight / min_weight / max_weight`,
+// src/score/llm/mod.rs:663-688).  No arithmetic for it exists in the reference, so everything here is
+// BUILD-DEFINED and parity is unpinned by construction; the device part is kept policy-free:
+//
+//   table_norm_kernel    1 / |row| of the resident table, once at load.
+//   table_scores_kernel  cosine of every table row against up to kTableQB prompt embeddings per pass;
+//                        HBM-bound stream over the table (one warp per row, 128-bit loads).
+//   table_topk_part/merge_kernel  the `top` best rows per prompt (ties -> lowest row): per-chunk top lists
+//                        held in registers, then one merge CTA per prompt.
+//
+// The weight policy itself (similarity-weighted local quality of each LLM, scaled around base, clamped
+// to [min, max]) is a few flops per LLM and runs in table_weights_kernel.
+#pragma once
+
+#include "../../include/lwc_b200.h"
+#include "score_common.cuh"
+
+namespace lwc {
+
+constexpr int kTableQB = 8;     // prompt embeddings per scoring pass
+constexpr int kTableMaxTop = 64;
+constexpr int kTableRows = 4;   // table rows per warp step of the score pass
+
+__global__ void __launch_bounds__(256)
+table_norm_kernel(const float *__restrict__ T, float *__restrict__ inv_norm, long long Tn, int D) {
+    const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= Tn) return;
+    const float *e = T + (size_t)row * D;
+    float ss = 0.f;
+    for (int k = lane; k < D; k += 32) ss = fmaf(e[k], e[k], ss);
+    ss = warp_sum(ss);
+    if (lane == 0) inv_norm[row] = ss > 0.f ? 1.0f / sqrtf(ss) : 0.f;
+}
+
+// scores[b][t] = <q_b, T_t> / (|q_b| |T_t|) for b < nq <= kTableQB.  q in shared memory.
+__global__ void __launch_bounds__(256)
+table_scores_kernel(const float *__restrict__ T, const float *__restrict__ inv_norm, const float *__restrict__ q,
+                    float *__restrict__ scores, long long Tn, int D, int nq) {
+    extern __shared__ float q_s[]; // [nq][D] then [nq] inverse norms
+    float *qn = q_s + (size_t)nq * D;
+    for (int i = threadIdx.x; i < nq * D; i += blockDim.x) q_s[i] = q[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp < nq) {
+        float ss = 0.f;
+        for (int k = lane; k < D; k += 32) ss = fmaf(q_s[warp * D + k], q_s[warp * D + k], ss);
+        ss = warp_sum(ss);
+        if (lane == 0) qn[warp] = ss > 0.f ? 1.0f / sqrtf(ss) : 0.f;
+    }
+    __syncthreads();
+    const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(T) & 15u) == 0);
+    // kTableRows consecutive rows per warp step: every prompt value read from shared memory is used for
+    // all of them, so the pass stays HBM-bound instead of shared-memory-bound.
+    const long long groups = (Tn + kTableRows - 1) / kTableRows;
+    for (long long g = (long long)blockIdx.x * (blockDim.x >> 5) + warp; g < groups;
+         g += (long long)gridDim.x * (blockDim.x >> 5)) {
+        const long long row0 = g * kTableRows;
+        const float *e[kTableRows];
+#pragma unroll
+        for (int r = 0; r < kTableRows; ++r) e[r] = T + (size_t)(row0 + r < Tn ? row0 + r : Tn - 1) * D;
+        float acc[kTableRows][kTableQB];
+#pragma unroll
+        for (int r = 0; r < kTableRows; ++r)
+#pragma unroll
+            for (int b = 0; b < kTableQB; ++b) acc[r][b] = 0.f;
+        if (vec) {
+#pragma unroll 2
+            for (int k = lane * 4; k < D; k += 128) {
+                float4 x[kTableRows];
+#pragma unroll
+                for (int r = 0; r < kTableRows; ++r) x[r] = ld_stream_f4(e[r] + k);
+#pragma unroll
+                for (int b = 0; b < kTableQB; ++b)
+                    if (b < nq) {
+                        const float4 y = *reinterpret_cast<const float4 *>(q_s + b * D + k);
+#pragma unroll
+                        for (int r = 0; r < kTableRows; ++r)
+                            acc[r][b] = fmaf(x[r].x, y.x, fmaf(x[r].y, y.y, fmaf(x[r].z, y.z, fmaf(x[r].w, y.w, acc[r][b]))));
+                    }
+            }
+        } else {
+            for (int k = lane; k < D; k += 32) {
+                float x[kTableRows];
+#pragma unroll
+                for (int r = 0; r < kTableRows; ++r) x[r] = e[r][k];
+#pragma unroll
+                for (int b = 0; b < kTableQB; ++b)
+                    if (b < nq) {
+                        const float y = q_s[b * D + k];
+#pragma unroll
+                        for (int r = 0; r < kTableRows; ++r) acc[r][b] = fmaf(x[r], y, acc[r][b]);
+                    }
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < kTableRows; ++r) {
+            if (row0 + r >= Tn) break;
+            const float rn = inv_norm[row0 + r];
+#pragma unroll
+            for (int b = 0; b < kTableQB; ++b)
+                if (b < nq) {
+                    const float sdot = warp_sum(acc[r][b]);
+                    if (lane == 0) scores[(size_t)b * Tn + row0 + r] = sdot * rn * qn[b];
+                }
+        }
+    }
+}
+
+// Block arg-max of (value, row) pairs, larger value first, lower row on ties; every thread gets the result.
+__device__ __forceinline__ void block_argmax(float &best, long long &arg, float *s_val, long long *s_arg) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(kFullMask, best, o);
+        const long long oa = __shfl_xor_sync(kFullMask, arg, o);
+        if (ob > best || (ob == best && oa < arg)) best = ob, arg = oa;
+    }
+    if (lane == 0) s_val[warp] = best, s_arg[warp] = arg;
+    __syncthreads();
+    best = lane < nwarp ? s_val[lane] : -INFINITY;
+    arg = lane < nwarp ? s_arg[lane] : 0x7fffffffffffffffLL;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(kFullMask, best, o);
+        const long long oa = __shfl_xor_sync(kFullMask, arg, o);
+        if (ob > best || (ob == best && oa < arg)) best = ob, arg = oa;
+    }
+    __syncthreads(); // s_val / s_arg are free for the next round
+}
+
+constexpr int kTopkPerThread = 8;
+constexpr int kTopkChunk = 1024 * kTopkPerThread; // table rows per CTA of the first top-k level
+
+// Level 1: grid (chunks, nq).  Each CTA holds its chunk of one prompt's scores in registers and extracts
+// the chunk's `top` best (value, row) pairs in `top` rounds of block arg-max.  cand_*: [nq][chunks][top].
+__global__ void __launch_bounds__(1024)
+table_topk_part_kernel(const float *__restrict__ scores, long long Tn, int top, float *__restrict__ cand_val,
+                       int32_t *__restrict__ cand_idx) {
+    __shared__ float s_val[32];
+    __shared__ long long s_arg[32];
+    const float *sc = scores + (size_t)blockIdx.y * Tn;
+    const long long row0 = (long long)blockIdx.x * kTopkChunk;
+    float v[kTopkPerThread];
+#pragma unroll
+    for (int j = 0; j < kTopkPerThread; ++j) {
+        const long long t = row0 + j * 1024 + threadIdx.x;
+        v[j] = t < Tn ? sc[t] : -INFINITY;
+    }
+    const size_t out = ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * top;
+    for (int k = 0; k < top; ++k) {
+        float best = -INFINITY;
+        long long arg = 0x7fffffffffffffffLL;
+#pragma unroll
+        for (int j = 0; j < kTopkPerThread; ++j)
+            if (v[j] > best) best = v[j], arg = row0 + j * 1024 + threadIdx.x; // rows grow with j: first maximum kept
+        block_argmax(best, arg, s_val, s_arg);
+        const bool found = best > -INFINITY;
+        if (threadIdx.x == 0) {
+            cand_val[out + k] = found ? best : -INFINITY;
+            cand_idx[out + k] = found ? (int32_t)arg : -1;
+        }
+        if (found) {
+            const long long off = arg - row0;
+            if ((int)(off & 1023) == (int)threadIdx.x) {
+#pragma unroll
+                for (int j = 0; j < kTopkPerThread; ++j)
+                    if (j == (int)(off >> 10)) v[j] = -INFINITY;
+            }
+        }
+    }
+}
+
+// Level 2: one CTA per prompt merges its ncand = chunks * top candidates (cand_val is destroyed).
+// idx/sim: [nq][top]; -1 / 0 past the table's size.
+__global__ void __launch_bounds__(1024)
+table_topk_merge_kernel(float *__restrict__ cand_val, const int32_t *__restrict__ cand_idx, long long ncand, int top,
+                        int32_t *__restrict__ idx, float *__restrict__ sim) {
+    __shared__ float s_val[32];
+    __shared__ long long s_arg[32];
+    float *cv = cand_val + (size_t)blockIdx.x * ncand;
+    const int32_t *ci = cand_idx + (size_t)blockIdx.x * ncand;
+    for (int k = 0; k < top; ++k) {
+        float best = -INFINITY;
+        long long arg = 0x7fffffffffffffffLL; // table row; candidate slots are ordered by row inside a chunk only
+        long long slot = -1;
+        for (long long c = threadIdx.x; c < ncand; c += blockDim.x) {
+            const float v = cv[c];
+            const long long r = ci[c];
+            if (r >= 0 && (v > best || (v == best && r < arg))) best = v, arg = r, slot = c;
+        }
+        const long long mine = arg;
+        block_argmax(best, arg, s_val, s_arg);
+        const bool found = best > -INFINITY;
+        if (found && mine == arg && slot >= 0) cv[slot] = -INFINITY; // rows are unique across candidates
+        if (threadIdx.x == 0) {
+            idx[(size_t)blockIdx.x * top + k] = found ? (int32_t)arg : -1;
+            sim[(size_t)blockIdx.x * top + k] = found ? best : 0.f;
+        }
+        __syncthreads();
+    }
+}
+
+// weights[b][m] = clamp(base_m * rho_m / mean_m'(rho_m'), min_m, max_m) with
+// rho_m = sum_k max(sim_k, 0) * Q[idx_k][m] / sum_k max(sim_k, 0) over the `top` neighbours;
+// base_m when there is no positive neighbour or mean(rho) == 0.  One warp per prompt.
+__global__ void __launch_bounds__(128)
+table_weights_kernel(const int32_t *__restrict__ idx, const float *__restrict__ sim, const float *__restrict__ Q,
+                     const float *__restrict__ base, const float *__restrict__ minw, const float *__restrict__ maxw,
+                     float *__restrict__ weights, int nq, int top, int M) {
+    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (b >= nq) return;
+    float ssum = 0.f;
+    for (int k = 0; k < top; ++k) {
+        const int t = idx[(size_t)b * top + k];
+        if (t >= 0) ssum += fmaxf(sim[(size_t)b * top + k], 0.f);
+    }
+    float rho[(LWC_MAX_VOTERS + 31) / 32];
+    float part = 0.f;
+#pragma unroll
+    for (int j = 0; j < (LWC_MAX_VOTERS + 31) / 32; ++j) {
+        const int m = j * 32 + lane;
+        float r = 0.f;
+        if (m < M && ssum > 0.f) {
+            for (int k = 0; k < top; ++k) {
+                const int t = idx[(size_t)b * top + k];
+                if (t >= 0) r = fmaf(fmaxf(sim[(size_t)b * top + k], 0.f), Q[(size_t)t * M + m], r);
+            }
+            r /= ssum;
+        }
+        rho[j] = r;
+        part += (m < M) ? r : 0.f;
+    }
+    const float mean = warp_sum(part) / (float)M;
+#pragma unroll
+    for (int j = 0; j < (LWC_MAX_VOTERS + 31) / 32; ++j) {
+        const int m = j * 32 + lane;
+        if (m < M) {
+            float wv = base[m];
+            if (ssum > 0.f && mean > 0.f) wv = base[m] * (rho[j] / mean);
+            weights[(size_t)b * M + m] = fminf(fmaxf(wv, minw[m]), maxw[m]);
+        }
+    }
+}
+
+} // namespace lwc

@@ -98,6 +98,10 @@ def load_library():
     L.lwc_pool_p2p_attach.restype = i32
     L.lwc_comm_destroy.argtypes = [vp]
     L.lwc_comm_destroy.restype = i32
+    L.lwc_table_load.argtypes = [vp, vp, vp, ctypes.c_int64, i32, i32]
+    L.lwc_table_load.restype = i32
+    L.lwc_table_weights.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, vp, vp]
+    L.lwc_table_weights.restype = i32
     L.lwc_stage_f64.argtypes = [vp, vp, ctypes.c_size_t, vp]
     L.lwc_stage_f64.restype = i32
     _lib = L
@@ -319,6 +323,28 @@ class Context:
         self._check(self.lib.lwc_vote_from_logprobs(self.handle, rows, top, n_choices, _np_ptr(lp), _np_ptr(lf),
                                                     _np_ptr(V), MEM_HOST, None))
         return V
+
+    def table_load(self, T, Q):
+        """lwc_table_load: keep a training table ([rows, D] prompt embeddings, [rows, M] per-LLM quality) on the GPU."""
+        T = np.ascontiguousarray(T, dtype=np.float32)
+        Q = np.ascontiguousarray(Q, dtype=np.float32)
+        assert T.ndim == 2 and Q.ndim == 2 and T.shape[0] == Q.shape[0]
+        self._table_shape = (T.shape[0], T.shape[1], Q.shape[1])
+        self._check(self.lib.lwc_table_load(self.handle, _np_ptr(T), _np_ptr(Q), ctypes.c_int64(T.shape[0]),
+                                            T.shape[1], Q.shape[1]))
+
+    def table_weights(self, q, top, base, minw, maxw):
+        """lwc_table_weights: per-prompt LLM weights from the `top` nearest rows of the loaded table."""
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        base, minw, maxw = (np.ascontiguousarray(a, dtype=np.float32) for a in (base, minw, maxw))
+        B = q.shape[0]
+        M = getattr(self, "_table_shape", (0, 0, base.size))[2]
+        weights = np.zeros((B, M), np.float32)
+        idx = np.zeros((B, max(top, 1)), np.int32)
+        sim = np.zeros((B, max(top, 1)), np.float32)
+        self._check(self.lib.lwc_table_weights(self.handle, _np_ptr(q), B, top, _np_ptr(base), _np_ptr(minw),
+                                               _np_ptr(maxw), _np_ptr(weights), _np_ptr(idx), _np_ptr(sim)))
+        return weights, idx, sim
 
     def stage_f64(self, src, dst):
         src = np.ascontiguousarray(src, dtype=np.float64)

@@ -173,5 +173,25 @@ def vote_from_logprobs(n_choices, logprobs, leaves):
     return vote
 
 
+def table_weights(T, Q, q, top, base, minw, maxw):
+    T = np.ascontiguousarray(T, dtype=np.float32)
+    Q = np.ascontiguousarray(Q, dtype=np.float32)
+    q = np.ascontiguousarray(q, dtype=np.float32)
+    base, minw, maxw = (np.ascontiguousarray(a, dtype=np.float32) for a in (base, minw, maxw))
+    rows, D = T.shape
+    M = Q.shape[1]
+    B = q.shape[0]
+    weights = np.empty((B, M), np.float64)
+    idx = np.empty((B, top), np.int32)
+    sim = np.empty((B, top), np.float64)
+    f = ctypes.c_float
+    rc = lib().lwc_oracle_table_weights(ctypes.c_int64(rows), D, M, _ptr(T, f), _ptr(Q, f), B, _ptr(q, f), top,
+                                        _ptr(base, f), _ptr(minw, f), _ptr(maxw, f), _ptr(weights, ctypes.c_double),
+                                        _ptr(idx, ctypes.c_int32), _ptr(sim, ctypes.c_double))
+    if rc:
+        raise ValueError("invalid table limits")
+    return weights, idx, sim
+
+
 def num_threads() -> int:
     return lib().lwc_oracle_num_threads()

@@ -522,3 +522,65 @@ int lwc_oracle_vote_from_logprobs(int n, int n_top, const double *logprob, const
     for (int i = 0; i < n; i++) vote[i] /= sum;
     return 0;
 }
+
+/* ------------------------------------------------------------------ training-table weights (8f2) */
+
+int lwc_oracle_table_weights(int64_t rows, int D, int M, const float *T, const float *Q, int n_prompts,
+                             const float *q, int top, const float *base, const float *minw, const float *maxw,
+                             double *weights, int32_t *top_idx, double *top_sim) {
+    /* The reference has no arithmetic here (weight.rs:99-117 is `unimplemented!()`): this restates
+     * the BUILD's definition (include/lwc_b200.h, lwc_table_weights) in f64 so the CUDA path has
+     * an independent checker.  Limits follow llm/mod.rs:671-687, `top >= 1` model/mod.rs:292-297. */
+    if (rows < 1 || top < 1) return 1;
+    for (int m = 0; m < M; m++)
+        if (!(minw[m] > 0.f) || !(base[m] >= minw[m]) || !(base[m] <= maxw[m])) return 1;
+    double *sc = (double *)malloc(sizeof(double) * (size_t)rows);
+    double *rn = (double *)malloc(sizeof(double) * (size_t)rows);
+    double *rho = (double *)malloc(sizeof(double) * (size_t)M);
+    for (int64_t t = 0; t < rows; t++) {
+        double ss = 0.0;
+        for (int k = 0; k < D; k++) ss += (double)T[t * D + k] * (double)T[t * D + k];
+        rn[t] = ss > 0.0 ? 1.0 / sqrt(ss) : 0.0;
+    }
+    for (int p = 0; p < n_prompts; p++) {
+        const float *qp = q + (size_t)p * D;
+        double qq = 0.0;
+        for (int k = 0; k < D; k++) qq += (double)qp[k] * (double)qp[k];
+        double qn = qq > 0.0 ? 1.0 / sqrt(qq) : 0.0;
+        for (int64_t t = 0; t < rows; t++) {
+            double d = 0.0;
+            for (int k = 0; k < D; k++) d += (double)T[t * D + k] * (double)qp[k];
+            sc[t] = d * rn[t] * qn;
+        }
+        double ssum = 0.0;
+        for (int m = 0; m < M; m++) rho[m] = 0.0;
+        for (int k = 0; k < top; k++) {
+            int64_t arg = -1;
+            double best = -INFINITY;
+            for (int64_t t = 0; t < rows; t++)
+                if (sc[t] > best) best = sc[t], arg = t;
+            top_idx[(size_t)p * top + k] = (int32_t)arg;
+            top_sim[(size_t)p * top + k] = arg >= 0 ? best : 0.0;
+            if (arg < 0) continue;
+            sc[arg] = -INFINITY;
+            double s = best > 0.0 ? best : 0.0;
+            ssum += s;
+            for (int m = 0; m < M; m++) rho[m] += s * (double)Q[arg * M + m];
+        }
+        double mean = 0.0;
+        for (int m = 0; m < M; m++) {
+            if (ssum > 0.0) rho[m] /= ssum;
+            mean += rho[m];
+        }
+        mean /= (double)M;
+        for (int m = 0; m < M; m++) {
+            double w = base[m];
+            if (ssum > 0.0 && mean > 0.0) w = (double)base[m] * (rho[m] / mean);
+            if (w < minw[m]) w = minw[m];
+            if (w > maxw[m]) w = maxw[m];
+            weights[(size_t)p * M + m] = w;
+        }
+    }
+    free(sc), free(rn), free(rho);
+    return 0;
+}

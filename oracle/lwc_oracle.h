@@ -85,6 +85,13 @@ int lwc_oracle_pool_f64(int64_t N, int D, int M, int method, const float *E, con
 int lwc_oracle_vote_from_logprobs(int n_choices, int n_top, const double *logprob, const int32_t *leaf,
                                   double *vote);
 
+/* f64 restatement of the BUILD-DEFINED training-table weight policy (include/lwc_b200.h,
+ * lwc_table_weights; the reference slot weight.rs:99-117 is unimplemented, so this checks the CUDA
+ * path against its own specification, not against the reference).  Returns 1 on invalid limits. */
+int lwc_oracle_table_weights(int64_t rows, int D, int M, const float *T, const float *Q, int n_prompts,
+                             const float *q, int top, const float *base, const float *minw, const float *maxw,
+                             double *weights, int32_t *top_idx, double *top_sim);
+
 /* Seconds the last lwc_oracle_score_port call spent in its compute phase (the fp32 -> Decimal
  * conversion of the synthetic inputs excluded: in the reference those arrive as Decimals). */
 double lwc_oracle_port_last_seconds(void);

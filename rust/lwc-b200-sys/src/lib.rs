@@ -113,4 +113,17 @@ extern "C" {
         memory: i32,
         stream: *mut c_void,
     ) -> i32;
+    pub fn lwc_table_load(ctx: *mut lwc_ctx, T: *const f32, Q: *const f32, rows: i64, D: i32, M: i32) -> i32;
+    pub fn lwc_table_weights(
+        ctx: *mut lwc_ctx,
+        q: *const f32,
+        n_prompts: i32,
+        top: i32,
+        base: *const f32,
+        minw: *const f32,
+        maxw: *const f32,
+        weights: *mut f32,
+        top_idx: *mut i32,
+        top_sim: *mut f32,
+    ) -> i32;
 }
