@@ -1,4 +1,5 @@
 // lwc_table_api.cu -- C ABI of the training-table weight lookup (BUILD-DEFINED, see table.cuh).
+#include <cstdlib>
 #include <cstring>
 
 #include "lwc_internal.hpp"
@@ -78,23 +79,40 @@ int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32
     CUDA_TRY(ctx, cudaMemcpyAsync(sb + o_lim, base, (size_t)M * 4, cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(sb + o_lim + (size_t)M * 4, minw, (size_t)M * 4, cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(sb + o_lim + (size_t)2 * M * 4, maxw, (size_t)M * 4, cudaMemcpyHostToDevice, st));
-    const size_t smem = ((size_t)QB * D + QB) * 4;
-    static bool configured[64] = {false};
-    if (smem > 48 * 1024 && !configured[ctx->device & 63]) {
-        CUDA_TRY(ctx, cudaFuncSetAttribute(lwc::table_scores_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           ctx->max_smem_optin));
-        configured[ctx->device & 63] = true;
-    }
+    // Route: the bulk-copy ring when the rows are 16-byte multiples and a ring of RS-row slots fits beside the
+    // prompt tile; else the direct-load kernel.  LWC_TABLE_IMPL=direct forces the latter (tests).
+    int RS = 0;
+    const char *impl = getenv("LWC_TABLE_IMPL");
+    if (D % 4 == 0 && !(impl && !strcmp(impl, "direct")))
+        for (int rs = 4; rs >= 1 && !RS; rs >>= 1)
+            if (lwc::table_ring_smem(rs, D, QB) <= (size_t)ctx->max_smem_optin) RS = rs;
+    const size_t smem = RS ? lwc::table_ring_smem(RS, D, QB) : ((size_t)QB * D + QB) * 4;
     if (smem > (size_t)ctx->max_smem_optin)
         return fail(ctx, LWC_ERR_INVALID, "lwc_table_weights: D=%d too large for the prompt tile in shared memory", D);
+    const void *fn = RS == 4   ? (const void *)lwc::table_scores_ring_kernel<4>
+                     : RS == 2 ? (const void *)lwc::table_scores_ring_kernel<2>
+                     : RS == 1 ? (const void *)lwc::table_scores_ring_kernel<1>
+                               : (const void *)lwc::table_scores_kernel;
+    if (smem > 48 * 1024) CUDA_TRY(ctx, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     for (int b0 = 0; b0 < n_prompts; b0 += QB) {
         const int nq = n_prompts - b0 < QB ? n_prompts - b0 : QB;
         CUDA_TRY(ctx, cudaMemcpyAsync(sb + o_q, q + (size_t)b0 * D, (size_t)nq * D * 4, cudaMemcpyHostToDevice, st));
-        long long blocks = (Tn + 8 * lwc::kTableRows - 1) / (8 * lwc::kTableRows);
-        if (blocks > 8LL * ctx->sm_count) blocks = 8LL * ctx->sm_count;
-        lwc::table_scores_kernel<<<(unsigned)blocks, 256, ((size_t)nq * D + nq) * 4, st>>>(
-            static_cast<const float *>(ctx->table_buf[0]), static_cast<const float *>(ctx->table_buf[1]),
-            reinterpret_cast<const float *>(sb + o_q), static_cast<float *>(ctx->table_buf[3]), Tn, D, nq);
+        const float *Td = static_cast<const float *>(ctx->table_buf[0]), *rn = static_cast<const float *>(ctx->table_buf[1]);
+        const float *qd = reinterpret_cast<const float *>(sb + o_q);
+        float *scd = reinterpret_cast<float *>(s3);
+        if (RS) {
+            const long long groups = (Tn + RS - 1) / RS;
+            const unsigned grid = (unsigned)(groups < ctx->sm_count ? groups : ctx->sm_count);
+            const unsigned thr = lwc::kTableRingThreads;
+            const size_t sm = lwc::table_ring_smem(RS, D, nq);
+            if (RS == 4) lwc::table_scores_ring_kernel<4><<<grid, thr, sm, st>>>(Td, rn, qd, scd, Tn, D, nq);
+            else if (RS == 2) lwc::table_scores_ring_kernel<2><<<grid, thr, sm, st>>>(Td, rn, qd, scd, Tn, D, nq);
+            else lwc::table_scores_ring_kernel<1><<<grid, thr, sm, st>>>(Td, rn, qd, scd, Tn, D, nq);
+        } else {
+            long long blocks = (Tn + 8 * lwc::kTableRows - 1) / (8 * lwc::kTableRows);
+            if (blocks > 8LL * ctx->sm_count) blocks = 8LL * ctx->sm_count;
+            lwc::table_scores_kernel<<<(unsigned)blocks, 256, ((size_t)nq * D + nq) * 4, st>>>(Td, rn, qd, scd, Tn, D, nq);
+        }
         lwc::table_topk_part_kernel<<<dim3((unsigned)chunks, nq), 1024, 0, st>>>(
             reinterpret_cast<const float *>(s3), Tn, top, reinterpret_cast<float *>(s3 + o_cv),
             reinterpret_cast<int32_t *>(s3 + o_cv + cand_bytes));

@@ -16,6 +16,7 @@
 
 #include "../../include/lwc_b200.h"
 #include "score_common.cuh"
+#include "score_stream.cuh" // mbarrier / bulk-copy helpers
 
 namespace lwc {
 
@@ -108,6 +109,139 @@ table_scores_kernel(const float *__restrict__ T, const float *__restrict__ inv_n
         }
     }
 }
+
+// The same pass as a persistent producer/consumer pipeline (the route for D % 4 == 0 tables whose ring fits):
+// warp 0 streams groups of RS consecutive table rows (one contiguous cp.async.bulk each) into a ring of
+// kTableSlots slots; slot s belongs to the consumer warp PAIR (2s+1, 2s+2) outright -- both warps wait on
+// full[s] and arrive on empty[s] every lap, so each observes every phase of its barriers.  The pair splits
+// the columns (alternate 128-float chunks), every prompt value read from shared memory is used for all RS
+// rows, and the RS x kTableQB dot products stay in registers; the odd warp hands its partial sums to the even
+// one through a lap-parity double buffer.  kTableSlots * RS * D * 4 bytes are in flight per SM at all times.
+constexpr int kTableSlots = 7;
+constexpr int kTableRingThreads = (2 * kTableSlots + 1) * 32;
+
+struct TableRingSmem { // byte offsets inside the dynamic shared memory
+    size_t qn, bars, part, ring, total;
+    __host__ __device__ TableRingSmem(int RS, int D, int nq) {
+        qn = (size_t)nq * D * 4;
+        bars = qn + kTableQB * 4;                 // full[slots], empty[slots], pair[slots]
+        part = bars + 3 * kTableSlots * 8;        // [slots][2][32] floats
+        ring = (part + kTableSlots * 2 * 32 * 4 + 127) & ~(size_t)127;
+        total = ring + (size_t)kTableSlots * RS * D * 4;
+    }
+};
+
+// Sum V per-lane values across the warp; afterwards lane l holds the total of value l >> (5 - log2 V).
+template <int V>
+__device__ __forceinline__ float warp_transpose_sum(float (&v)[V], int lane) {
+    static_assert(V == 8 || V == 16 || V == 32, "V");
+    int off = 16;
+#pragma unroll
+    for (int n = V / 2; n >= 1; n >>= 1, off >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < n; ++i) {
+            const float send = up ? v[i] : v[i + n];
+            const float keep = up ? v[i + n] : v[i];
+            v[i] = keep + __shfl_xor_sync(kFullMask, send, off);
+        }
+    }
+    float r = v[0];
+    for (; off >= 1; off >>= 1) r += __shfl_xor_sync(kFullMask, r, off);
+    return r;
+}
+
+template <int RS>
+__global__ void __launch_bounds__(kTableRingThreads, 1)
+table_scores_ring_kernel(const float *__restrict__ T, const float *__restrict__ inv_norm, const float *__restrict__ q,
+                         float *__restrict__ scores, long long Tn, int D, int nq) {
+    extern __shared__ __align__(128) unsigned char tsm[];
+    const TableRingSmem L(RS, D, nq);
+    float *q_s = reinterpret_cast<float *>(tsm); // [nq][D]
+    float *qn = reinterpret_cast<float *>(tsm + L.qn);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(tsm + L.bars);
+    float *part = reinterpret_cast<float *>(tsm + L.part);
+    float *ring = reinterpret_cast<float *>(tsm + L.ring); // [slots][RS][D]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < nq * D; i += blockDim.x) q_s[i] = q[i];
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kTableSlots; ++s) {
+            mbar_init(smem_u32(bars + s), 1);                   // full: the producer's expect_tx arrive
+            mbar_init(smem_u32(bars + kTableSlots + s), 2);     // empty: both warps of the pair
+            mbar_init(smem_u32(bars + 2 * kTableSlots + s), 1); // pair: the odd warp's partial sums are posted
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp < nq) {
+        float ss = 0.f;
+        for (int k = lane; k < D; k += 32) ss = fmaf(q_s[warp * D + k], q_s[warp * D + k], ss);
+        ss = warp_sum(ss);
+        if (lane == 0) qn[warp] = ss > 0.f ? 1.0f / sqrtf(ss) : 0.f;
+    }
+    __syncthreads();
+    const long long groups = (Tn + RS - 1) / RS;
+    const long long njobs = groups > blockIdx.x ? (groups - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const size_t slot_floats = (size_t)RS * D;
+    if (warp == 0) {
+        if (lane == 0) {
+            for (long long j = 0; j < njobs; ++j) {
+                const int slot = (int)(j % kTableSlots);
+                const long long lap = j / kTableSlots;
+                if (lap > 0) mbar_wait(smem_u32(bars + kTableSlots + slot), (uint32_t)((lap - 1) & 1));
+                const long long row0 = (blockIdx.x + j * gridDim.x) * RS;
+                const int nrows = (int)(Tn - row0 < RS ? Tn - row0 : RS);
+                const uint32_t bytes = (uint32_t)((size_t)nrows * D * 4);
+                mbar_arrive_expect_tx(smem_u32(bars + slot), bytes);
+                bulk_g2s(smem_u32(ring + slot * slot_floats), T + (size_t)row0 * D, bytes, smem_u32(bars + slot));
+            }
+        }
+        return;
+    }
+    const int slot = (warp - 1) >> 1, half = (warp - 1) & 1;
+    const float *xs = ring + slot * slot_floats;
+    constexpr int V = RS * kTableQB;
+    for (long long j = slot, lap = 0; j < njobs; j += kTableSlots, ++lap) {
+        mbar_wait(smem_u32(bars + slot), (uint32_t)(lap & 1));
+        float acc[V];
+#pragma unroll
+        for (int a = 0; a < V; ++a) acc[a] = 0.f;
+#pragma unroll 2
+        for (int k = half * 128 + lane * 4; k < D; k += 256) {
+            float4 x[RS];
+#pragma unroll
+            for (int r = 0; r < RS; ++r) x[r] = *reinterpret_cast<const float4 *>(xs + (size_t)r * D + k);
+#pragma unroll
+            for (int b = 0; b < kTableQB; ++b)
+                if (b < nq) {
+                    const float4 y = *reinterpret_cast<const float4 *>(q_s + b * D + k);
+#pragma unroll
+                    for (int r = 0; r < RS; ++r)
+                        acc[r * kTableQB + b] =
+                            fmaf(x[r].x, y.x, fmaf(x[r].y, y.y, fmaf(x[r].z, y.z, fmaf(x[r].w, y.w, acc[r * kTableQB + b]))));
+                }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(bars + kTableSlots + slot)); // this warp no longer reads the slot
+        float tot = warp_transpose_sum<V>(acc, lane);
+        float *pp = part + ((size_t)slot * 2 + (lap & 1)) * 32;
+        if (half == 1) {
+            pp[lane] = tot;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(bars + 2 * kTableSlots + slot));
+        } else {
+            mbar_wait(smem_u32(bars + 2 * kTableSlots + slot), (uint32_t)(lap & 1));
+            tot += pp[lane];
+            const int a = lane >> (V == 32 ? 0 : V == 16 ? 1 : 2);
+            const int r = a / kTableQB, b = a % kTableQB;
+            const long long row = (blockIdx.x + j * gridDim.x) * RS + r;
+            const bool first = (lane & ((32 / V) - 1)) == 0;
+            if (first && row < Tn && b < nq) scores[(size_t)b * Tn + row] = tot * inv_norm[row] * qn[b];
+        }
+    }
+}
+
+static inline size_t table_ring_smem(int RS, int D, int nq) { return TableRingSmem(RS, D, nq).total; }
 
 // Block arg-max of (value, row) pairs, larger value first, lower row on ties; every thread gets the result.
 __device__ __forceinline__ void block_argmax(float &best, long long &arg, float *s_val, long long *s_arg) {

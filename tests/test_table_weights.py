@@ -47,9 +47,15 @@ def test_oracle_table_weights_properties(oracle):
 @pytest.mark.gpu
 @pytest.mark.parametrize("rows,D,M,nq,top", [
     (1, 8, 1, 1, 1), (5, 7, 3, 2, 8), (1000, 64, 8, 19, 5), (4099, 1536, 16, 9, 16), (20000, 384, 128, 8, 64),
+    (3001, 3072, 4, 3, 4), (50001, 1536, 16, 8, 16),
 ])
-def test_table_weights_match_oracle(oracle, rows, D, M, nq, top):
+@pytest.mark.parametrize("impl", ["ring", "direct"])
+def test_table_weights_match_oracle(oracle, monkeypatch, rows, D, M, nq, top, impl):
     import lwc_b200
+    if impl == "direct":
+        monkeypatch.setenv("LWC_TABLE_IMPL", "direct")
+    else:
+        monkeypatch.delenv("LWC_TABLE_IMPL", raising=False)
     T, Q, q, base, minw, maxw = make_table(rows + top, rows, D, M, nq)
     with lwc_b200.Context(0) as ctx:
         ctx.table_load(T, Q)
@@ -89,6 +95,17 @@ def test_table_weights_errors_and_reload(oracle):
         wz, _, sz = ctx.table_weights(np.zeros((1, 32), np.float32), 2, base, minw, maxw)
         np.testing.assert_array_equal(wz[0], base)
         assert (sz == 0).all()
+        # both score-pass routes agree (their summation orders differ)
+        import os
+        os.environ["LWC_TABLE_IMPL"] = "direct"
+        try:
+            wd, idd, simd = ctx.table_weights(q, 2, base, minw, maxw)
+        finally:
+            del os.environ["LWC_TABLE_IMPL"]
+        wr, idr, simr = ctx.table_weights(q, 2, base, minw, maxw)
+        assert (idd == idr).all()
+        np.testing.assert_allclose(simd, simr, atol=SIM_ATOL, rtol=0)
+        np.testing.assert_allclose(wd, wr, rtol=W_RTOL)
         # reload a smaller table; results follow the new table, and the run is reproducible
         ctx.table_load(T[:10], Q[:10])
         w2, i2, _ = ctx.table_weights(q, 2, base, minw, maxw)
