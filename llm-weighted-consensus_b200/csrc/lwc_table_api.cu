@@ -70,7 +70,7 @@ int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32
     // scratch: [3] scores [QB][Tn] | per-chunk candidates (value, row) [QB][chunks][top]; [4] q | idx | sim | limits | weights for one pass
     const long long chunks = (Tn + lwc::kTopkChunk - 1) / lwc::kTopkChunk;
     const size_t o_cv = ((size_t)QB * Tn * 4 + 255) & ~(size_t)255, cand_bytes = (size_t)QB * chunks * top * 4;
-    if ((rc = table_ensure(ctx, 3, o_cv + 2 * cand_bytes))) return rc;
+    if ((rc = table_ensure(ctx, 3, o_cv + 4 * cand_bytes))) return rc; // two (value, row) list buffers
     char *s3 = static_cast<char *>(ctx->table_buf[3]);
     const size_t o_q = 0, o_idx = (size_t)QB * D * 4, o_sim = o_idx + (size_t)QB * top * 4, o_lim = o_sim + (size_t)QB * top * 4,
                  o_w = o_lim + (size_t)3 * M * 4, total = o_w + (size_t)QB * M * 4;
@@ -113,19 +113,33 @@ int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32
             if (blocks > 8LL * ctx->sm_count) blocks = 8LL * ctx->sm_count;
             lwc::table_scores_kernel<<<(unsigned)blocks, 256, ((size_t)nq * D + nq) * 4, st>>>(Td, rn, qd, scd, Tn, D, nq);
         }
-        lwc::table_topk_part_kernel<<<dim3((unsigned)chunks, nq), 1024, 0, st>>>(
-            reinterpret_cast<const float *>(s3), Tn, top, reinterpret_cast<float *>(s3 + o_cv),
-            reinterpret_cast<int32_t *>(s3 + o_cv + cand_bytes));
-        lwc::table_topk_merge_kernel<<<nq, 1024, 0, st>>>(reinterpret_cast<float *>(s3 + o_cv),
-                                                          reinterpret_cast<const int32_t *>(s3 + o_cv + cand_bytes), chunks * top, top,
-                                                          reinterpret_cast<int32_t *>(sb + o_idx), reinterpret_cast<float *>(sb + o_sim));
+        { // top-k reduction tree: scores -> per-chunk lists -> ... -> idx / sim
+            const float *iv = scd;
+            const int32_t *ii = nullptr;
+            long long n = Tn;
+            int level = 0;
+            for (;; ++level) {
+                const long long ch = (n + lwc::kTopkChunk - 1) / lwc::kTopkChunk;
+                const bool last = ch == 1;
+                float *ov = reinterpret_cast<float *>(s3 + o_cv + (size_t)(level & 1) * 2 * cand_bytes);
+                int32_t *oi = reinterpret_cast<int32_t *>(s3 + o_cv + (size_t)(level & 1) * 2 * cand_bytes + cand_bytes);
+                int32_t *fi = last ? reinterpret_cast<int32_t *>(sb + o_idx) : nullptr;
+                float *fs = last ? reinterpret_cast<float *>(sb + o_sim) : nullptr;
+                const dim3 grid((unsigned)ch, nq);
+                if (ii) lwc::table_topk_kernel<true><<<grid, lwc::kTopkThreads, 0, st>>>(iv, ii, n, top, ov, oi, fi, fs);
+                else lwc::table_topk_kernel<false><<<grid, lwc::kTopkThreads, 0, st>>>(iv, ii, n, top, ov, oi, fi, fs);
+                ctx->launches++;
+                if (last) break;
+                iv = ov, ii = oi, n = ch * top;
+            }
+        }
         lwc::table_weights_kernel<<<(nq + 3) / 4, 128, 0, st>>>(
             reinterpret_cast<const int32_t *>(sb + o_idx), reinterpret_cast<const float *>(sb + o_sim),
             static_cast<const float *>(ctx->table_buf[2]), reinterpret_cast<const float *>(sb + o_lim),
             reinterpret_cast<const float *>(sb + o_lim + (size_t)M * 4), reinterpret_cast<const float *>(sb + o_lim + (size_t)2 * M * 4),
             reinterpret_cast<float *>(sb + o_w), nq, top, M);
         CUDA_TRY(ctx, cudaGetLastError());
-        ctx->launches += 4;
+        ctx->launches += 2;
         CUDA_TRY(ctx, cudaMemcpyAsync(weights + (size_t)b0 * M, sb + o_w, (size_t)nq * M * 4, cudaMemcpyDeviceToHost, st));
         if (top_idx) CUDA_TRY(ctx, cudaMemcpyAsync(top_idx + (size_t)b0 * top, sb + o_idx, (size_t)nq * top * 4, cudaMemcpyDeviceToHost, st));
         if (top_sim) CUDA_TRY(ctx, cudaMemcpyAsync(top_sim + (size_t)b0 * top, sb + o_sim, (size_t)nq * top * 4, cudaMemcpyDeviceToHost, st));

@@ -7,8 +7,8 @@
 //   table_norm_kernel    1 / |row| of the resident table, once at load.
 //   table_scores_kernel  cosine of every table row against up to kTableQB prompt embeddings per pass;
 //                        HBM-bound stream over the table (one warp per row, 128-bit loads).
-//   table_topk_part/merge_kernel  the `top` best rows per prompt (ties -> lowest row): per-chunk top lists
-//                        held in registers, then one merge CTA per prompt.
+//   table_topk_kernel    the `top` best rows per prompt (ties -> lowest row): a reduction tree of per-chunk
+//                        top lists held in registers.
 //
 // The weight policy itself (similarity-weighted local quality of each LLM, scaled around base, clamped
 // to [min, max]) is a few flops per LLM and runs in table_weights_kernel.
@@ -243,97 +243,81 @@ table_scores_ring_kernel(const float *__restrict__ T, const float *__restrict__ 
 
 static inline size_t table_ring_smem(int RS, int D, int nq) { return TableRingSmem(RS, D, nq).total; }
 
-// Block arg-max of (value, row) pairs, larger value first, lower row on ties; every thread gets the result.
-__device__ __forceinline__ void block_argmax(float &best, long long &arg, float *s_val, long long *s_arg) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const float ob = __shfl_xor_sync(kFullMask, best, o);
-        const long long oa = __shfl_xor_sync(kFullMask, arg, o);
-        if (ob > best || (ob == best && oa < arg)) best = ob, arg = oa;
-    }
-    if (lane == 0) s_val[warp] = best, s_arg[warp] = arg;
-    __syncthreads();
-    best = lane < nwarp ? s_val[lane] : -INFINITY;
-    arg = lane < nwarp ? s_arg[lane] : 0x7fffffffffffffffLL;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const float ob = __shfl_xor_sync(kFullMask, best, o);
-        const long long oa = __shfl_xor_sync(kFullMask, arg, o);
-        if (ob > best || (ob == best && oa < arg)) best = ob, arg = oa;
-    }
-    __syncthreads(); // s_val / s_arg are free for the next round
-}
+// Top-k by repeated arg-max, as a reduction tree.  Grid (chunks, nq), kTopkThreads threads; a CTA holds its
+// chunk of kTopkChunk (value, position) entries of one prompt in registers (kTopkPerThread per thread, each
+// thread caching its own best), and extracts the chunk's `top` best in `top` rounds: warp arg-max by
+// shuffles, one barrier, then every warp reduces the per-warp winners redundantly (round-parity double buffer,
+// so one barrier per round).  Ties go to the lowest position, which is the lowest table row at every level:
+// level 1 reads raw scores (position = row), later levels read the previous level's lists, which keep equal
+// values in row order.  Output [nq][chunks][top] (value, row), -inf / -1 when the chunk runs out; the last
+// level (one chunk) writes idx / sim ([nq][top], -1 / 0 past the table's size) instead.
+constexpr int kTopkThreads = 256;
+constexpr int kTopkPerThread = 32;
+constexpr int kTopkChunk = kTopkThreads * kTopkPerThread;
 
-constexpr int kTopkPerThread = 8;
-constexpr int kTopkChunk = 1024 * kTopkPerThread; // table rows per CTA of the first top-k level
-
-// Level 1: grid (chunks, nq).  Each CTA holds its chunk of one prompt's scores in registers and extracts
-// the chunk's `top` best (value, row) pairs in `top` rounds of block arg-max.  cand_*: [nq][chunks][top].
-__global__ void __launch_bounds__(1024)
-table_topk_part_kernel(const float *__restrict__ scores, long long Tn, int top, float *__restrict__ cand_val,
-                       int32_t *__restrict__ cand_idx) {
-    __shared__ float s_val[32];
-    __shared__ long long s_arg[32];
-    const float *sc = scores + (size_t)blockIdx.y * Tn;
-    const long long row0 = (long long)blockIdx.x * kTopkChunk;
+template <bool HAS_IDX>
+__global__ void __launch_bounds__(kTopkThreads)
+table_topk_kernel(const float *__restrict__ in_val, const int32_t *__restrict__ in_idx, long long n_in, int top,
+                  float *__restrict__ out_val, int32_t *__restrict__ out_idx, int32_t *__restrict__ fin_idx,
+                  float *__restrict__ fin_sim) {
+    constexpr int NW = kTopkThreads / 32;
+    __shared__ float s_val[2][NW];
+    __shared__ int s_pos[2][NW];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float *iv = in_val + (size_t)blockIdx.y * n_in;
+    const long long e0 = (long long)blockIdx.x * kTopkChunk;
     float v[kTopkPerThread];
 #pragma unroll
     for (int j = 0; j < kTopkPerThread; ++j) {
-        const long long t = row0 + j * 1024 + threadIdx.x;
-        v[j] = t < Tn ? sc[t] : -INFINITY;
+        const long long e = e0 + j * kTopkThreads + threadIdx.x;
+        v[j] = e < n_in ? iv[e] : -INFINITY;
     }
+    float bv = -INFINITY;
+    int bj = 0;
+#pragma unroll
+    for (int j = 0; j < kTopkPerThread; ++j)
+        if (v[j] > bv) bv = v[j], bj = j; // positions grow with j: the first maximum is kept
     const size_t out = ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * top;
     for (int k = 0; k < top; ++k) {
-        float best = -INFINITY;
-        long long arg = 0x7fffffffffffffffLL;
+        float best = bv;
+        int pos = bj * kTopkThreads + threadIdx.x;
 #pragma unroll
-        for (int j = 0; j < kTopkPerThread; ++j)
-            if (v[j] > best) best = v[j], arg = row0 + j * 1024 + threadIdx.x; // rows grow with j: first maximum kept
-        block_argmax(best, arg, s_val, s_arg);
-        const bool found = best > -INFINITY;
-        if (threadIdx.x == 0) {
-            cand_val[out + k] = found ? best : -INFINITY;
-            cand_idx[out + k] = found ? (int32_t)arg : -1;
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(kFullMask, best, o);
+            const int op = __shfl_xor_sync(kFullMask, pos, o);
+            if (ob > best || (ob == best && op < pos)) best = ob, pos = op;
         }
-        if (found) {
-            const long long off = arg - row0;
-            if ((int)(off & 1023) == (int)threadIdx.x) {
+        if (lane == 0) s_val[k & 1][warp] = best, s_pos[k & 1][warp] = pos;
+        __syncthreads();
+        best = lane < NW ? s_val[k & 1][lane] : -INFINITY;
+        pos = lane < NW ? s_pos[k & 1][lane] : 0x7fffffff;
 #pragma unroll
-                for (int j = 0; j < kTopkPerThread; ++j)
-                    if (j == (int)(off >> 10)) v[j] = -INFINITY;
+        for (int o = NW / 2; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(kFullMask, best, o);
+            const int op = __shfl_xor_sync(kFullMask, pos, o);
+            if (ob > best || (ob == best && op < pos)) best = ob, pos = op;
+        }
+        best = __shfl_sync(kFullMask, best, 0);
+        pos = __shfl_sync(kFullMask, pos, 0);
+        const bool found = best > -INFINITY;
+        if (found && (pos & (kTopkThreads - 1)) == (int)threadIdx.x) { // the winner's owner: emit, mask, rescan
+            int32_t row;
+            if (HAS_IDX) row = in_idx[(size_t)blockIdx.y * n_in + e0 + pos];
+            else row = (int32_t)(e0 + pos);
+            if (fin_idx) fin_idx[(size_t)blockIdx.y * top + k] = row, fin_sim[(size_t)blockIdx.y * top + k] = best;
+            else out_val[out + k] = best, out_idx[out + k] = row;
+            const int wj = pos / kTopkThreads;
+            bv = -INFINITY, bj = 0;
+#pragma unroll
+            for (int j = 0; j < kTopkPerThread; ++j) {
+                if (j == wj) v[j] = -INFINITY;
+                if (v[j] > bv) bv = v[j], bj = j;
             }
         }
-    }
-}
-
-// Level 2: one CTA per prompt merges its ncand = chunks * top candidates (cand_val is destroyed).
-// idx/sim: [nq][top]; -1 / 0 past the table's size.
-__global__ void __launch_bounds__(1024)
-table_topk_merge_kernel(float *__restrict__ cand_val, const int32_t *__restrict__ cand_idx, long long ncand, int top,
-                        int32_t *__restrict__ idx, float *__restrict__ sim) {
-    __shared__ float s_val[32];
-    __shared__ long long s_arg[32];
-    float *cv = cand_val + (size_t)blockIdx.x * ncand;
-    const int32_t *ci = cand_idx + (size_t)blockIdx.x * ncand;
-    for (int k = 0; k < top; ++k) {
-        float best = -INFINITY;
-        long long arg = 0x7fffffffffffffffLL; // table row; candidate slots are ordered by row inside a chunk only
-        long long slot = -1;
-        for (long long c = threadIdx.x; c < ncand; c += blockDim.x) {
-            const float v = cv[c];
-            const long long r = ci[c];
-            if (r >= 0 && (v > best || (v == best && r < arg))) best = v, arg = r, slot = c;
+        if (!found && threadIdx.x == 0) {
+            if (fin_idx) fin_idx[(size_t)blockIdx.y * top + k] = -1, fin_sim[(size_t)blockIdx.y * top + k] = 0.f;
+            else out_val[out + k] = -INFINITY, out_idx[out + k] = -1;
         }
-        const long long mine = arg;
-        block_argmax(best, arg, s_val, s_arg);
-        const bool found = best > -INFINITY;
-        if (found && mine == arg && slot >= 0) cv[slot] = -INFINITY; // rows are unique across candidates
-        if (threadIdx.x == 0) {
-            idx[(size_t)blockIdx.x * top + k] = found ? (int32_t)arg : -1;
-            sim[(size_t)blockIdx.x * top + k] = found ? best : 0.f;
-        }
-        __syncthreads();
     }
 }
 

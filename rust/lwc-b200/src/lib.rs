@@ -110,9 +110,36 @@ pub fn merge_error_codes(codes: &[Option<u16>]) -> Option<u16> {
     }
 }
 
+impl Context {
+    /// `lwc_table_load`: keep the training table (past prompt embeddings `t [rows][d]`, per-LLM quality
+    /// `q [rows][m]`) resident on the GPU.
+    pub fn table_load(&self, t: &[f32], q: &[f32], rows: usize, d: usize, m: usize) -> Result<(), ResponseError> {
+        assert!(t.len() == rows * d && q.len() == rows * m);
+        match unsafe { sys::lwc_table_load(self.0, t.as_ptr(), q.as_ptr(), rows as i64, d as i32, m as i32) } {
+            0 => Ok(()),
+            rc => Err(response_error(rc, self.0)),
+        }
+    }
+
+    /// `lwc_table_weights` for one prompt embedding: one weight per LLM from the `top` nearest table rows.
+    pub fn table_weights(&self, prompt: &[f32], top: usize, base: &[f32], min: &[f32], max: &[f32]) -> Result<Vec<f32>, ResponseError> {
+        let mut w = vec![0f32; base.len()];
+        let rc = unsafe {
+            sys::lwc_table_weights(self.0, prompt.as_ptr(), 1, top as i32, base.as_ptr(), min.as_ptr(), max.as_ptr(),
+                w.as_mut_ptr(), std::ptr::null_mut(), std::ptr::null_mut())
+        };
+        if rc != 0 {
+            return Err(response_error(rc, self.0));
+        }
+        Ok(w)
+    }
+}
+
 /// Fills the `FTRAININGTABLE` slot of `score::completions::Client` (client.rs:27-33), whose shipped
-/// implementation is `unimplemented!()` (weight.rs:99-117).  `embed` is the user's embeddings call;
-/// the per-LLM weights come from the model's `base_weight` (src/score/llm/mod.rs:663-688).
+/// implementation is `unimplemented!()` (weight.rs:99-117).  `embed` is the user's embeddings call for the
+/// prompt; the table was loaded into the context with `table_load`; `top` comes from the model's
+/// `WeightTrainingTable { top, .. }` (src/score/model/mod.rs:278-306) and the limits from each LLM's
+/// `base_weight / min_weight / max_weight` (src/score/llm/mod.rs:663-688).
 pub struct B200TrainingTableFetcher<F> {
     pub ctx: Arc<Context>,
     pub embed: F,
@@ -133,11 +160,22 @@ where
         model: score::model::Model,
     ) -> Result<(Vec<Decimal>, score::completions::weight::TrainingTableData), ResponseError> {
         let embeddings_response = (self.embed)(request).await?;
-        let weights = model
+        let limits: Vec<[f32; 3]> = model
             .llms
             .iter()
-            .map(|llm| llm.base.weight.weight_training_table().map(|w| w.base_weight).unwrap_or(Decimal::ONE))
+            .map(|llm| match llm.base.weight.weight_training_table() {
+                Some(w) => [w.base_weight, w.min_weight, w.max_weight].map(|d| d.to_f32().unwrap_or(1.0)),
+                None => [1.0; 3],
+            })
             .collect();
+        let col = |i: usize| limits.iter().map(|l| l[i]).collect::<Vec<f32>>();
+        let top = match &model.weight {
+            score::model::Weight::TrainingTable(t) => t.top,
+            _ => 1,
+        };
+        let prompt: Vec<f32> = embeddings_response.data.first().map(|e| e.embedding.iter().map(|&x| x as f32).collect()).unwrap_or_default();
+        let weights = self.ctx.table_weights(&prompt, top, &col(0), &col(1), &col(2))?;
+        let weights = weights.into_iter().map(|w| Decimal::from_f32(w).unwrap_or(Decimal::ONE)).collect();
         Ok((weights, score::completions::weight::TrainingTableData { embeddings_response }))
     }
 }

@@ -115,3 +115,33 @@ def test_table_weights_errors_and_reload(oracle):
         we, ie, _ = oracle.table_weights(T[:10], Q[:10], q, 2, base, minw, maxw)
         assert (i2 == ie).all()
         np.testing.assert_allclose(w2, we, rtol=W_RTOL)
+
+
+@pytest.mark.gpu
+def test_table_topk_tree_three_levels_and_ties():
+    """1.1M rows with top 64 needs three levels of the top-k tree; identical rows must come out lowest row first."""
+    import lwc_b200
+    rows, top = 1_100_000, 64
+    rng = np.random.default_rng(11)
+    perm = rng.permutation(rows)
+    T = np.zeros((rows, 4), np.float32)
+    T[:, 0] = 1.0
+    T[:, 1] = perm * 0.01          # cosine against [1, 0, 0, 0] falls strictly with perm
+    Q = np.ones((rows, 2), np.float32)
+    q = np.array([[1, 0, 0, 0], [2, -2, 0, 0]], np.float32)
+    one = np.ones(2, np.float32)
+    expect = np.argsort(perm)[:top]
+    with lwc_b200.Context(0) as ctx:
+        ctx.table_load(T, Q)
+        _, idx, sim = ctx.table_weights(q, top, one, one, one)
+        assert (idx[0] == expect).all() and (idx[1] == expect).all()
+        assert (np.diff(sim, axis=1) < 0).all()
+        Tt = np.ones((20000, 8), np.float32)
+        Tt[::2] *= 4.0  # same direction, other length: the cosine does not change
+        ctx.table_load(Tt, np.ones((20000, 2), np.float32))
+        _, idx, sim = ctx.table_weights(np.ones((1, 8), np.float32), top, one, one, one)
+        assert (idx[0] == np.arange(top)).all()
+        # fewer rows than `top`: the tail is -1 / 0
+        ctx.table_load(Tt[:5], np.ones((5, 2), np.float32))
+        _, idx, sim = ctx.table_weights(np.ones((1, 8), np.float32), 8, one, one, one)
+        assert (idx[0] == [0, 1, 2, 3, 4, -1, -1, -1]).all() and (sim[0, 5:] == 0).all()
