@@ -43,6 +43,26 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 // (value, index) arg-max with ties resolved to the lowest index.
+// Sum V per-lane values across the warp; afterwards lane l holds the total of value l >> (5 - log2 V).
+template <int V>
+__device__ __forceinline__ float warp_transpose_sum(float (&v)[V], int lane) {
+    static_assert(V == 8 || V == 16 || V == 32, "V");
+    int off = 16;
+#pragma unroll
+    for (int n = V / 2; n >= 1; n >>= 1, off >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < n; ++i) {
+            const float send = up ? v[i] : v[i + n];
+            const float keep = up ? v[i + n] : v[i];
+            v[i] = keep + __shfl_xor_sync(kFullMask, send, off);
+        }
+    }
+    float r = v[0];
+    for (; off >= 1; off >>= 1) r += __shfl_xor_sync(kFullMask, r, off);
+    return r;
+}
+
 __device__ __forceinline__ void warp_argmax(float &v, int &idx) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {

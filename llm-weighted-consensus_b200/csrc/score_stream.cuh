@@ -66,6 +66,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         if (clock64() - t0 > 4000000000LL) __trap(); // ~2 s at 2 GHz
     }
 }
+// The same wait for warps that expect to wait long: every try_wait of a spinning warp is a shared-memory
+// wavefront (ncu: ten spinning warps took 16 % of the SM's shared-memory pipe in score_tc_kernel<x3>), so
+// back off between polls.
+__device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity, unsigned ns) {
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    do {
+        __nanosleep(ns);
+        if (clock64() - t0 > 4000000000LL) __trap();
+    } while (!mbar_try_wait(bar, parity));
+}
 // TMA: one [1][rows][cols] box of a rank-3 tensor map -> shared memory, completion on `bar`.
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm, int c0, int c1, int c2, uint32_t bar) {
     asm volatile(

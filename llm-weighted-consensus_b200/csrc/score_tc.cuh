@@ -22,16 +22,22 @@
 //
 // X3 = false: inputs are read by the tensor core as TF32 (the low 13 mantissa bits of each fp32 are
 // ignored) -- the `precision = LWC_PREC_TF32` route with the stated 2e-3 confidence tolerance.
-// X3 = true: fp32-grade result.  Four extra "transform" warps (2, 3, 8, 9) turn every landed slab x
-// into its remainder lo = x - trunc_tf32(x) in a twin slab (same swizzled layout, so the transform is
-// purely elementwise), and the issuer runs three MMAs per K step into the SAME accumulator:
-// hi.hi^T + hi.lo^T + lo.hi^T  (hi is what the tensor core sees of x; lo.lo^T < 2^-20 is dropped).
+// X3 = true: fp32-grade result.  Four extra "transform" warps (2, 3, 8, 9) turn every landed stage x
+// into its remainder lo = x - trunc_tf32(x) in a slot of a separate two-slot lo ring (same swizzled layout, so
+// the transform is purely elementwise; a lo stage lives only from transform to MMA, so two slots are enough
+// and the rest of shared memory holds raw stages in flight from HBM), and the issuer runs TWO MMAs per K step: X += hi.hi^T and, into a second
+// accumulator, Y += hi.lo^T  (hi is what the tensor core sees of x).  S = X + Y + Y^T (lo.lo^T < 2^-20 is
+// dropped): the third product of the classic scheme is the transpose of the second, so it is never computed
+// -- the epilogue folds Y in twice, once along its row and once, through a warp transpose-sum, along its
+// column.  That takes the operand reads from 3 x 2 to 2 x 2 slab volumes per slab.
 // The tensor core's fp32 accumulator truncates when it aligns addends: over the 1,152 MMAs of a
 // D = 3072 request the diagonal drifted by ~1e-5 relative (measured), too much for the 1e-5 bar.  So the
-// X3 route accumulates in CHUNKS of kTcChunkStages stages: the two TMEM accumulators alternate per
+// X3 route accumulates in CHUNKS of kTcChunkSlabs slabs: the two TMEM accumulators alternate per
 // chunk, and the epilogue threads add each finished chunk into fp32 registers (round-to-nearest adds),
-// which bounds every in-TMEM accumulation chain to < 100 MMAs.
-// Three MMAs per step make this route shared-memory-bandwidth bound (operand reads), below HBM speed.
+// which bounds every in-TMEM accumulation chain to < 100 MMAs.  Y is ~2^-11 of X, so its drift does not
+// matter and it accumulates over the whole request (its own two TMEM accumulators alternate per request).
+// This route is shared-memory-bandwidth bound (TMA write + transform read/write + operand reads = 7 slab
+// volumes per slab; an M = N = 128 tf32 MMA at full rate alone reads 126 B/clk of the 128 B/clk), below HBM speed.
 // Bound: HBM (64 flop/B at N = 128 against a TF32 balance of > 150 flop/B).
 #pragma once
 
@@ -45,7 +51,8 @@ constexpr int kTcThreads = 256;   // TF32 route: producer, issuer, TMEM allocato
 constexpr int kTcThreadsX3 = 320; // + warps 8, 9; warps 2, 3, 8, 9 transform
 constexpr int kTcSlabBytes = 128 * 128;  // one [128 rows x 32 fp32] operand slab, SWIZZLE_128B
 constexpr int kTcMaxStages = 8;
-constexpr int kTcChunkStages = 4; // X3: stages per in-TMEM accumulation chunk
+constexpr int kTcLoSlots = 2;     // X3: ring of remainder (lo) stages; a lo stage lives only from transform to MMA
+constexpr int kTcChunkSlabs = 8;  // X3: operand slabs (32 MMAs into X) per in-TMEM accumulation chunk
 #ifndef LWC_TC_ROUND
 #define LWC_TC_ROUND 0u
 #endif
@@ -121,19 +128,23 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
     extern __shared__ __align__(1024) unsigned char smem_tc[];
     const int KO = geo.ko, S = geo.stages;
     const int rawb = KO * kTcSlabBytes;            // bytes the TMA box delivers per stage
-    const int stageb = (X3 ? 2 : 1) * rawb;        // X3: [raw slabs][lo slabs]
+    const int stageb = rawb;
     constexpr int NTW = 4;                         // transform warps (X3 only)
     // dynamic shared memory is only guaranteed 16-byte aligned: SWIZZLE_128B tiles need 1024
     unsigned char *ring = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_tc) + 1023) & ~(uintptr_t)1023);
-    float *u_s = reinterpret_cast<float *>(ring + (size_t)S * stageb); // [128] t_i / n_i
+    unsigned char *lo_ring = ring + (size_t)S * stageb;                // X3: kTcLoSlots stages of remainders
+    float *u_s = reinterpret_cast<float *>(lo_ring + (X3 ? (size_t)kTcLoSlots * rawb : 0)); // [128] t_i / n_i
     float *cf_s = u_s + 128;                                          // [128] confidences
     float *part = cf_s + 128;                                         // [16] block-reduction scratch
     int *ipart = reinterpret_cast<int *>(part + 16);                  // [8]
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(ipart + 8);    // [2]
-    uint64_t *bars = reinterpret_cast<uint64_t *>(tmem_slot + 2);     // full[S], empty[S], tfull[2], tempty[2], ready[S]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(tmem_slot + 2);     // full[S], empty[S], tfull[2], tempty[2], ready[S], yempty[2]
     const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * kTcMaxStages;
     const uint32_t tfull0 = empty0 + 8 * kTcMaxStages, tempty0 = tfull0 + 16;
     const uint32_t ready0 = tempty0 + 16; // X3: lo slabs of the stage are written and visible to the tensor core
+    const uint32_t yempty0 = ready0 + 8 * kTcMaxStages; // X3: the request-long Y accumulator has been read
+    const uint32_t lofree0 = yempty0 + 16;              // X3: the MMAs that read a lo stage have completed
+    float *col_s = reinterpret_cast<float *>(bars + 3 * kTcMaxStages + 6 + kTcLoSlots); // X3: [4][128] column sums of u_i Y_ij per warp
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int N = p.N, D = p.D, M = p.M;
@@ -142,21 +153,27 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
     const int nreq = r_end - r_begin;
     const int nslab = D >> 5;                  // 32-column operand slabs per request (D % 32 == 0)
     const int spr = (nslab + KO - 1) / KO;     // stages per request
+    const int cst = kTcChunkSlabs / KO > 0 ? kTcChunkSlabs / KO : 1; // stages per accumulation chunk (X3)
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < S; ++s) {
             mbar_init(full0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, 1);
+        }
+        for (int s = 0; s < kTcLoSlots; ++s) {
             mbar_init(ready0 + 8 * s, NTW);
+            mbar_init(lofree0 + 8 * s, 1);
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(tfull0 + 8 * b, 1);
             mbar_init(tempty0 + 8 * b, 128);
+            mbar_init(yempty0 + 8 * b, 128);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 2) { // TMEM: 256 columns = two 128 x 128 fp32 accumulators
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256)
+    constexpr uint32_t kTmemCols = X3 ? 512 : 256; // two 128 x 128 fp32 accumulators (X3: two for X, two for Y)
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -173,7 +190,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
             uint32_t phase = 0;
             for (int q = 0; q < nreq; ++q)
                 for (int s = 0; s < spr; ++s) {
-                    mbar_wait(empty0 + 8 * slot, phase ^ 1u);
+                    mbar_wait_backoff(empty0 + 8 * slot, phase ^ 1u, 40);
                     mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)rawb); // OOB zero-fill counts too
                     tma_load_4d(ring_u32 + slot * stageb, &tmE, 0, 0, s * KO, r_begin + q, full0 + 8 * slot);
                     if (++slot == S) {
@@ -191,14 +208,20 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
             int slot = 0;
             uint32_t phase = 0;
             uint32_t tile = 0; // accumulator hand-offs so far: one per request (TF32) or per chunk (X3)
+            uint32_t g = 0;    // X3: stages so far; lo slot g % kTcLoSlots
             for (int q = 0; q < nreq; ++q) {
                 uint32_t ab = tile & 1u;
                 mbar_wait(tempty0 + 8 * ab, ((tile >> 1) & 1u) ^ 1u); // accumulator drained by the epilogue
                 tc_fence_after();
                 uint32_t d_tmem = tmem_base + ab * 128u;
-                uint32_t acc = 0;
+                uint32_t acc = 0, accy = 0;
+                const uint32_t y_tmem = tmem_base + 256u + (uint32_t)(q & 1) * 128u;
+                if (X3) {
+                    mbar_wait(yempty0 + 8 * (q & 1), (((uint32_t)q >> 1) & 1u) ^ 1u);
+                    tc_fence_after();
+                }
                 for (int s = 0; s < spr; ++s) {
-                    if (X3 && s > 0 && s % kTcChunkStages == 0) { // chunk boundary: hand over, switch accumulator
+                    if (X3 && s > 0 && s % cst == 0) { // chunk boundary: hand over, switch accumulator
                         umma_commit(tfull0 + 8 * ab);
                         ++tile;
                         ab = tile & 1u;
@@ -207,7 +230,9 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                         d_tmem = tmem_base + ab * 128u;
                         acc = 0;
                     }
-                    mbar_wait((X3 ? ready0 : full0) + 8 * slot, phase);
+                    const uint32_t ls = g % kTcLoSlots;
+                    if (X3) mbar_wait_backoff(ready0 + 8 * ls, (g / kTcLoSlots) & 1u, 20); // implies full[slot]
+                    else mbar_wait_backoff(full0 + 8 * slot, phase, 20);
                     tc_fence_after();
                     const int nk = min(KO, nslab - s * KO);
                     for (int k = 0; k < nk; ++k) {
@@ -217,14 +242,16 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                             const uint64_t hi = umma_desc_sw128(slab + kk * 32);
                             umma_tf32(d_tmem, hi, hi, idesc, acc);
                             if (X3) {
-                                const uint64_t lo = umma_desc_sw128(slab + rawb + kk * 32);
-                                umma_tf32(d_tmem, hi, lo, idesc, 1);
-                                umma_tf32(d_tmem, lo, hi, idesc, 1);
+                                const uint64_t lo = umma_desc_sw128(smem_u32(lo_ring) + ls * rawb + k * kTcSlabBytes + kk * 32);
+                                umma_tf32(y_tmem, hi, lo, idesc, accy);
+                                accy = 1;
                             }
                             acc = 1;
                         }
                     }
                     umma_commit(empty0 + 8 * slot); // stage reusable once these MMAs have read it
+                    if (X3) umma_commit(lofree0 + 8 * ls);
+                    ++g;
                     if (++slot == S) {
                         slot = 0;
                         phase ^= 1u;
@@ -239,27 +266,33 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         // ===================== transform: lo = x - trunc_tf32(x), slab by slab =====================
         const int tw = warp < 4 ? warp - 2 : warp - 6; // 0..3
         int slot = 0;
-        uint32_t phase = 0;
+        uint32_t phase = 0, g = 0;
         for (int q = 0; q < nreq; ++q)
-            for (int s = 0; s < spr; ++s) {
-                mbar_wait(full0 + 8 * slot, phase);
-                const float4 *src = reinterpret_cast<const float4 *>(ring + (size_t)slot * stageb);
-                float4 *dst = reinterpret_cast<float4 *>(ring + (size_t)slot * stageb + rawb);
+            for (int s = 0; s < spr; ++s, ++g) {
+                const uint32_t ls = g % kTcLoSlots;
+                mbar_wait_backoff(lofree0 + 8 * ls, ((g / kTcLoSlots) & 1u) ^ 1u, 40);
+                mbar_wait_backoff(full0 + 8 * slot, phase, 40);
+                const uint32_t src = smem_u32(ring) + (uint32_t)slot * (uint32_t)stageb;
+                const uint32_t dst = smem_u32(lo_ring) + ls * (uint32_t)rawb;
                 const int n16 = rawb >> 4;
 #pragma unroll 4
                 for (int idx = tw * 32 + lane; idx < n16; idx += NTW * 32) {
-                    const float4 x = src[idx];
-                    float4 l;
+                    float4 x, l;
+                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                 : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w)
+                                 : "r"(src + (uint32_t)idx * 16u));
                     l.x = x.x - __uint_as_float((__float_as_uint(x.x) + kTcRound) & 0xffffe000u);
                     l.y = x.y - __uint_as_float((__float_as_uint(x.y) + kTcRound) & 0xffffe000u);
                     l.z = x.z - __uint_as_float((__float_as_uint(x.z) + kTcRound) & 0xffffe000u);
                     l.w = x.w - __uint_as_float((__float_as_uint(x.w) + kTcRound) & 0xffffe000u);
-                    dst[idx] = l;
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (uint32_t)idx * 16u), "f"(l.x), "f"(l.y),
+                                 "f"(l.z), "f"(l.w)
+                                 : "memory");
                 }
                 // generic-proxy writes must be visible to the tensor core (async proxy) before it is told
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
-                if (lane == 0) mbar_arrive(ready0 + 8 * slot);
+                if (lane == 0) mbar_arrive(ready0 + 8 * ls);
                 if (++slot == S) {
                     slot = 0;
                     phase ^= 1u;
@@ -272,7 +305,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         const bool act = i < N;
         const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
         uint32_t tile = 0;
-        const int nchunk = X3 ? (spr + kTcChunkStages - 1) / kTcChunkStages : 1;
+        const int nchunk = X3 ? (spr + cst - 1) / cst : 1;
         for (int q = 0; q < nreq; ++q) {
             const int r = r_begin + q;
             const float *Vr = p.V + (size_t)r * M * N;
@@ -295,7 +328,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                 for (int e = 0; e < 128; ++e) row[e] = 0.f;
                 for (int ch = 0; ch < nchunk; ++ch, ++tile) {
                     const uint32_t ab = tile & 1u;
-                    mbar_wait(tfull0 + 8 * ab, (tile >> 1) & 1u);
+                    mbar_wait_backoff(tfull0 + 8 * ab, (tile >> 1) & 1u, 200);
                     tc_fence_after();
                     const uint32_t row_addr = lane_addr + ab * 128u;
 #pragma unroll
@@ -307,18 +340,39 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                     tc_fence_before();
                     mbar_arrive(tempty0 + 8 * ab);
                 }
+                // the last chunk's commit covered every MMA of the request: Y = hi.lo^T is complete too
+                const uint32_t y_addr = lane_addr + 256u + (uint32_t)(q & 1) * 128u;
+                tmem_ld32(y_addr + (uint32_t)(ew * 32), v);
+                float yd = 0.f;
+#pragma unroll
+                for (int e = 0; e < 32; ++e) yd = (lane == e) ? v[e] : yd;
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
 #pragma unroll
                     for (int e = 0; e < 32; ++e) d = (c == ew && lane == e) ? row[c * 32 + e] : d;
+                d = fmaf(2.f, yd, d); // S_ii = X_ii + 2 Y_ii
                 rn = (act && d > 0.f) ? 1.0f / sqrtf(d) : 0.f;
-                u_s[i] = t * rn;
+                const float ui = t * rn;
+                u_s[i] = ui;
                 epi_sync();
+                // sum_j u_j S_ij = sum_j u_j (X_ij + Y_ij)  [own row]  +  sum_j u_j Y_ji  [column i of u_j-scaled Y]
 #pragma unroll
-                for (int e = 0; e < 128; ++e) acc = fmaf(u_s[e], row[e], acc);
+                for (int c = 0; c < 4; ++c) {
+                    tmem_ld32(y_addr + (uint32_t)(c * 32), v);
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) {
+                        acc = fmaf(u_s[c * 32 + e], row[c * 32 + e] + v[e], acc);
+                        v[e] *= ui;
+                    }
+                    col_s[ew * 128 + c * 32 + lane] = warp_transpose_sum<32>(v, lane); // rows of this warp, column 32c + lane
+                }
+                tc_fence_before();
+                mbar_arrive(yempty0 + 8 * (q & 1));
+                epi_sync();
+                acc += (col_s[i] + col_s[128 + i]) + (col_s[256 + i] + col_s[384 + i]);
             } else {
                 const uint32_t ab = tile & 1u;
-                mbar_wait(tfull0 + 8 * ab, (tile >> 1) & 1u);
+                mbar_wait_backoff(tfull0 + 8 * ab, (tile >> 1) & 1u, 200);
                 tc_fence_after();
                 const uint32_t row_addr = lane_addr + ab * 128u;
                 // diagonal: S_ii sits in column chunk `ew` at register index `lane`
@@ -404,12 +458,13 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
     __syncthreads();
     if (warp == 2) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
     }
 }
 
 inline size_t tc_smem_bytes(int ko, int stages, bool x3) {
-    return 1024 + (size_t)stages * ko * kTcSlabBytes * (x3 ? 2 : 1) + (128 + 128 + 16 + 8 + 2) * 4 + (3 * kTcMaxStages + 4) * 8 + 64;
+    return 1024 + (size_t)(stages + (x3 ? kTcLoSlots : 0)) * ko * kTcSlabBytes + (128 + 128 + 16 + 8 + 2) * 4 +
+           (3 * kTcMaxStages + 6 + kTcLoSlots) * 8 + (x3 ? 4 * 128 * 4 : 0) + 64;
 }
 
 } // namespace lwc

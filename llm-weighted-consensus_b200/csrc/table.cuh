@@ -131,26 +131,6 @@ struct TableRingSmem { // byte offsets inside the dynamic shared memory
     }
 };
 
-// Sum V per-lane values across the warp; afterwards lane l holds the total of value l >> (5 - log2 V).
-template <int V>
-__device__ __forceinline__ float warp_transpose_sum(float (&v)[V], int lane) {
-    static_assert(V == 8 || V == 16 || V == 32, "V");
-    int off = 16;
-#pragma unroll
-    for (int n = V / 2; n >= 1; n >>= 1, off >>= 1) {
-        const bool up = (lane & off) != 0;
-#pragma unroll
-        for (int i = 0; i < n; ++i) {
-            const float send = up ? v[i] : v[i + n];
-            const float keep = up ? v[i + n] : v[i];
-            v[i] = keep + __shfl_xor_sync(kFullMask, send, off);
-        }
-    }
-    float r = v[0];
-    for (; off >= 1; off >>= 1) r += __shfl_xor_sync(kFullMask, r, off);
-    return r;
-}
-
 template <int RS>
 __global__ void __launch_bounds__(kTableRingThreads, 1)
 table_scores_ring_kernel(const float *__restrict__ T, const float *__restrict__ inv_norm, const float *__restrict__ q,
