@@ -189,7 +189,8 @@ cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) 
         configured[ctx->device & 63] = true;
     }
     CUtensorMap tm;
-    if (!make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, geo.ko)) return cudaErrorInvalidValue;
+    // fp32-grade route: one box per slab (the slabs of a stage are interleaved with their remainder slabs)
+    if (!make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, X3 ? 1 : geo.ko)) return cudaErrorInvalidValue;
     const int grid = p.R < ctx->sm_count ? p.R : ctx->sm_count;
     lwc::score_tc_kernel<X3><<<grid, X3 ? lwc::kTcThreadsX3 : lwc::kTcThreads, lwc::tc_smem_bytes(geo.ko, geo.stages, X3), st>>>(
         tm, p, geo);

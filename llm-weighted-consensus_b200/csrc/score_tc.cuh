@@ -12,7 +12,7 @@
 //                    (profiles/r1_tma_probe2.txt): 32 KB boxes x 4 stages stream at 6.0 TB/s,
 //                    64 KB boxes x 3 stages at 6.58 TB/s.
 //   warp 1 (1 lane)  MMA issuer.  Per slab 4 x tcgen05.mma (M=128, N=128, K=8), the SAME shared
-//                    tile as A and as B descriptor; tcgen05.commit releases the stage; the last
+//                    tile as A and as B descriptor (X3: N=256, see below); tcgen05.commit releases the stage; the last
 //                    commit of a request signals the epilogue.  Two 128-column accumulators in
 //                    TMEM alternate, so request q+1 accumulates while q is being finalised.
 //   warps 4..7       epilogue: thread i owns TMEM lane i = row i of S (tcgen05.ld 32x32b).
@@ -22,23 +22,32 @@
 //
 // X3 = false: inputs are read by the tensor core as TF32 (the low 13 mantissa bits of each fp32 are
 // ignored) -- the `precision = LWC_PREC_TF32` route with the stated 2e-3 confidence tolerance.
-// X3 = true: fp32-grade result.  Four extra "transform" warps (2, 3, 8, 9) turn every landed stage x
-// into its remainder lo = x - trunc_tf32(x) in a slot of a separate two-slot lo ring (same swizzled layout, so
-// the transform is purely elementwise; a lo stage lives only from transform to MMA, so two slots are enough
-// and the rest of shared memory holds raw stages in flight from HBM), and the issuer runs TWO MMAs per K step: X += hi.hi^T and, into a second
-// accumulator, Y += hi.lo^T  (hi is what the tensor core sees of x).  S = X + Y + Y^T (lo.lo^T < 2^-20 is
-// dropped): the third product of the classic scheme is the transpose of the second, so it is never computed
-// -- the epilogue folds Y in twice, once along its row and once, through a warp transpose-sum, along its
-// column.  That takes the operand reads from 3 x 2 to 2 x 2 slab volumes per slab.
-// The tensor core's fp32 accumulator truncates when it aligns addends: over the 1,152 MMAs of a
-// D = 3072 request the diagonal drifted by ~1e-5 relative (measured), too much for the 1e-5 bar.  So the
-// X3 route accumulates in CHUNKS of kTcChunkSlabs slabs: the two TMEM accumulators alternate per
-// chunk, and the epilogue threads add each finished chunk into fp32 registers (round-to-nearest adds),
-// which bounds every in-TMEM accumulation chain to < 100 MMAs.  Y is ~2^-11 of X, so its drift does not
-// matter and it accumulates over the whole request (its own two TMEM accumulators alternate per request).
-// This route is shared-memory-bandwidth bound (TMA write + transform read/write + operand reads = 7 slab
-// volumes per slab; an M = N = 128 tf32 MMA at full rate alone reads 126 B/clk of the 128 B/clk), below HBM speed.
-// Bound: HBM (64 flop/B at N = 128 against a TF32 balance of > 150 flop/B).
+// X3 = true: fp32-grade result from two tf32 products per K step in ONE instruction.  With hi = trunc_tf32(x)
+// (what the tensor core sees of an fp32 operand -- measured: it truncates) and lo = x - hi,
+// S = X + Y + Y^T where X = hi.hi^T and Y = hi.lo^T (lo.lo^T < 2^-20 is dropped).  The third product of the
+// classic 3xTF32 scheme is the transpose of the second, so it is never computed: the epilogue folds Y in
+// twice, once along its row and once, through a warp transpose-sum, along its column.  Four "transform" warps
+// (2, 3, 8, 9) write lo of every landed slab into a twin slab right behind it (same swizzled layout, so the
+// transform is purely elementwise), and the issuer runs one M = 128, N = 256 MMA per K step whose B operand is
+// the 256-row pair [raw slab ; lo slab]: the accumulator tile is [X | Y] (2 x 256 TMEM columns, double buffered).
+// The raw slabs of a stage arrive as one-slab TMA boxes so that each can sit in front of its twin.
+// The tensor core's fp32 accumulator truncates when it aligns addends: over the MMAs of a D = 3072 request
+// the diagonal drifted by ~1e-5 relative (measured), too much for the 1e-5 bar.  So X accumulates in CHUNKS
+// of kTcChunkSlabs slabs: the two accumulators alternate per chunk and the epilogue threads add each finished X
+// into fp32 registers (round-to-nearest adds), which bounds every in-TMEM chain to 32 MMAs.  Y is ~2^-11 of X,
+// so its drift does not matter and it must NOT restart per chunk (there are no registers left to sum it in):
+// the MMAs therefore always accumulate, and the epilogue zeroes what has to restart with tcgen05.st -- the X
+// half after each chunk, the two Y halves (even chunks' Y in one accumulator, odd chunks' in the other) after
+// reading them at the end of the request.
+// This route is TENSOR-bound: a kind::tf32 MMA costs ~1.07 clk per (128-row x 8-deep) output column (measured:
+// N = 128 in 150 clk, N = 256 in 273 clk; ncu's tf32 peak is 1,024 FMA/clk/SM, a quarter of bf16), so the
+// 2 x 4 x 128 columns per slab take >= 1,024 clk against the ~600 clk a slab has at HBM speed.
+// History (cfg4, 8,192 requests): three N = 128 MMAs, all operands in shared memory 4.02 ms -> two MMAs with
+// the symmetric fold 3.6 ms -> A operands from tensor memory (tcgen05.st by row-loader warps, tcgen05.mma with
+// a TMEM A) 3.6 ms, which showed that shared-memory bandwidth was not the limit -> one N = 256 MMA 3.36 ms
+// = 0.94 of the tf32 tensor peak.  A faster fp32-grade route has to move the correction product to kind::f16
+// (bf16 lo x bf16 hi, 4x the rate); not built.
+// Bound: TF32 route HBM (tensor pipe ~85 % busy at HBM speed); X3 route tensor.
 #pragma once
 
 #include <cuda.h>
@@ -51,7 +60,6 @@ constexpr int kTcThreads = 256;   // TF32 route: producer, issuer, TMEM allocato
 constexpr int kTcThreadsX3 = 320; // + warps 8, 9; warps 2, 3, 8, 9 transform
 constexpr int kTcSlabBytes = 128 * 128;  // one [128 rows x 32 fp32] operand slab, SWIZZLE_128B
 constexpr int kTcMaxStages = 8;
-constexpr int kTcLoSlots = 2;     // X3: ring of remainder (lo) stages; a lo stage lives only from transform to MMA
 constexpr int kTcChunkSlabs = 8;  // X3: operand slabs (32 MMAs into X) per in-TMEM accumulation chunk
 #ifndef LWC_TC_ROUND
 #define LWC_TC_ROUND 0u
@@ -95,6 +103,18 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// 32 consecutive columns of this thread's TMEM lane <- registers.
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+          "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+          "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+          "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
 // All MMAs issued so far by this thread arrive on `bar` when they complete (implies fence::before_thread_sync).
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -127,13 +147,14 @@ __global__ void __launch_bounds__(X3 ? kTcThreadsX3 : kTcThreads, 1)
 score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, const TcGeom geo) {
     extern __shared__ __align__(1024) unsigned char smem_tc[];
     const int KO = geo.ko, S = geo.stages;
-    const int rawb = KO * kTcSlabBytes;            // bytes the TMA box delivers per stage
-    const int stageb = rawb;
+    // TF32 route: a stage is one TMA box of KO slabs.  X3: a stage is KO pairs [raw slab][lo slab], each pair
+    // the 256-row B operand of one N = 256 MMA; the raw slabs arrive as KO one-slab boxes.
+    constexpr int kSlabStride = (X3 ? 2 : 1) * kTcSlabBytes;
+    const int stageb = KO * kSlabStride;
     constexpr int NTW = 4;                         // transform warps (X3 only)
     // dynamic shared memory is only guaranteed 16-byte aligned: SWIZZLE_128B tiles need 1024
     unsigned char *ring = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_tc) + 1023) & ~(uintptr_t)1023);
-    unsigned char *lo_ring = ring + (size_t)S * stageb;                // X3: kTcLoSlots stages of remainders
-    float *u_s = reinterpret_cast<float *>(lo_ring + (X3 ? (size_t)kTcLoSlots * rawb : 0)); // [128] t_i / n_i
+    float *u_s = reinterpret_cast<float *>(ring + (size_t)S * stageb); // [128] t_i / n_i
     float *cf_s = u_s + 128;                                          // [128] confidences
     float *part = cf_s + 128;                                         // [16] block-reduction scratch
     int *ipart = reinterpret_cast<int *>(part + 16);                  // [8]
@@ -141,10 +162,9 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
     uint64_t *bars = reinterpret_cast<uint64_t *>(tmem_slot + 2);     // full[S], empty[S], tfull[2], tempty[2], ready[S], yempty[2]
     const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * kTcMaxStages;
     const uint32_t tfull0 = empty0 + 8 * kTcMaxStages, tempty0 = tfull0 + 16;
-    const uint32_t ready0 = tempty0 + 16; // X3: lo slabs of the stage are written and visible to the tensor core
-    const uint32_t yempty0 = ready0 + 8 * kTcMaxStages; // X3: the request-long Y accumulator has been read
-    const uint32_t lofree0 = yempty0 + 16;              // X3: the MMAs that read a lo stage have completed
-    float *col_s = reinterpret_cast<float *>(bars + 3 * kTcMaxStages + 6 + kTcLoSlots); // X3: [4][128] column sums of u_i Y_ij per warp
+    const uint32_t ready0 = tempty0 + 16; // X3: the stage's lo slabs are written and visible to the tensor core
+    const uint32_t yempty0 = ready0 + 8 * kTcMaxStages; // X3: both Y accumulators have been read and zeroed
+    float *col_s = reinterpret_cast<float *>(bars + 3 * kTcMaxStages + 6); // X3: [4][128] column sums of u_i Y_ij per warp
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int N = p.N, D = p.D, M = p.M;
@@ -159,19 +179,16 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         for (int s = 0; s < S; ++s) {
             mbar_init(full0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, 1);
-        }
-        for (int s = 0; s < kTcLoSlots; ++s) {
             mbar_init(ready0 + 8 * s, NTW);
-            mbar_init(lofree0 + 8 * s, 1);
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(tfull0 + 8 * b, 1);
             mbar_init(tempty0 + 8 * b, 128);
-            mbar_init(yempty0 + 8 * b, 128);
+            mbar_init(yempty0 + 8 * b, 128); // only [0] is used
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    constexpr uint32_t kTmemCols = X3 ? 512 : 256; // two 128 x 128 fp32 accumulators (X3: two for X, two for Y)
+    constexpr uint32_t kTmemCols = X3 ? 512 : 256; // two accumulators: 128 x 128 fp32, or X3: 128 x 256 = [X | Y]
     if (warp == 2) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols)
                      : "memory");
@@ -181,6 +198,20 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (X3) {
+        // X3 MMAs always accumulate (the N = 256 tile holds X, restarted per chunk, beside Y, which is not),
+        // so the epilogue threads zero what must restart; at the start, everything.
+        if (warp >= 4 && warp < 8) {
+            uint32_t z[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) z[e] = 0u;
+            for (int c = 0; c < 16; ++c) tmem_st32(tmem_base + ((uint32_t)((warp - 4) * 32) << 16) + (uint32_t)(c * 32), z);
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        }
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+    }
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -191,8 +222,16 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
             for (int q = 0; q < nreq; ++q)
                 for (int s = 0; s < spr; ++s) {
                     mbar_wait_backoff(empty0 + 8 * slot, phase ^ 1u, 40);
-                    mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)rawb); // OOB zero-fill counts too
-                    tma_load_4d(ring_u32 + slot * stageb, &tmE, 0, 0, s * KO, r_begin + q, full0 + 8 * slot);
+                    if (X3) { // one box per slab, into the first half of its [raw][lo] pair
+                        const int nk = min(KO, nslab - s * KO);
+                        mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)(nk * kTcSlabBytes));
+                        for (int k = 0; k < nk; ++k)
+                            tma_load_4d(ring_u32 + slot * stageb + k * kSlabStride, &tmE, 0, 0, s * KO + k, r_begin + q,
+                                        full0 + 8 * slot);
+                    } else {
+                        mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)(KO * kTcSlabBytes)); // OOB zero-fill counts too
+                        tma_load_4d(ring_u32 + slot * stageb, &tmE, 0, 0, s * KO, r_begin + q, full0 + 8 * slot);
+                    }
                     if (++slot == S) {
                         slot = 0;
                         phase ^= 1u;
@@ -204,20 +243,19 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         // ===================== MMA issuer =====================
         if (lane == 0) {
             const uint32_t ring_u32 = smem_u32(ring);
-            const uint32_t idesc = umma_idesc_tf32(128, 128);
+            const uint32_t idesc = umma_idesc_tf32(128, X3 ? 256 : 128);
+            constexpr uint32_t kAccCols = X3 ? 256u : 128u;
             int slot = 0;
             uint32_t phase = 0;
             uint32_t tile = 0; // accumulator hand-offs so far: one per request (TF32) or per chunk (X3)
-            uint32_t g = 0;    // X3: stages so far; lo slot g % kTcLoSlots
             for (int q = 0; q < nreq; ++q) {
                 uint32_t ab = tile & 1u;
                 mbar_wait(tempty0 + 8 * ab, ((tile >> 1) & 1u) ^ 1u); // accumulator drained by the epilogue
                 tc_fence_after();
-                uint32_t d_tmem = tmem_base + ab * 128u;
-                uint32_t acc = 0, accy = 0;
-                const uint32_t y_tmem = tmem_base + 256u + (uint32_t)(q & 1) * 128u;
-                if (X3) {
-                    mbar_wait(yempty0 + 8 * (q & 1), (((uint32_t)q >> 1) & 1u) ^ 1u);
+                uint32_t d_tmem = tmem_base + ab * kAccCols;
+                uint32_t acc = 0;
+                if (X3) { // both Y halves drained and zeroed by the epilogue of the previous request
+                    mbar_wait(yempty0, ((uint32_t)q & 1u) ^ 1u);
                     tc_fence_after();
                 }
                 for (int s = 0; s < spr; ++s) {
@@ -227,31 +265,23 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                         ab = tile & 1u;
                         mbar_wait(tempty0 + 8 * ab, ((tile >> 1) & 1u) ^ 1u);
                         tc_fence_after();
-                        d_tmem = tmem_base + ab * 128u;
-                        acc = 0;
+                        d_tmem = tmem_base + ab * kAccCols;
                     }
-                    const uint32_t ls = g % kTcLoSlots;
-                    if (X3) mbar_wait_backoff(ready0 + 8 * ls, (g / kTcLoSlots) & 1u, 20); // implies full[slot]
-                    else mbar_wait_backoff(full0 + 8 * slot, phase, 20);
+                    mbar_wait_backoff((X3 ? ready0 : full0) + 8 * slot, phase, 20); // X3: ready implies full
                     tc_fence_after();
                     const int nk = min(KO, nslab - s * KO);
                     for (int k = 0; k < nk; ++k) {
-                        const uint32_t slab = ring_u32 + slot * stageb + k * kTcSlabBytes;
+                        const uint32_t slab = ring_u32 + slot * stageb + k * kSlabStride;
 #pragma unroll
                         for (int kk = 0; kk < 4; ++kk) { // 4 x K=8 inside the 128-byte swizzle atom
-                            const uint64_t hi = umma_desc_sw128(slab + kk * 32);
-                            umma_tf32(d_tmem, hi, hi, idesc, acc);
-                            if (X3) {
-                                const uint64_t lo = umma_desc_sw128(smem_u32(lo_ring) + ls * rawb + k * kTcSlabBytes + kk * 32);
-                                umma_tf32(y_tmem, hi, lo, idesc, accy);
-                                accy = 1;
-                            }
+                            // A: the raw slab (hi to the tensor core).  B: the same start address -- 128 rows
+                            // (TF32 route: S += hi hi^T) or 256 rows = [raw ; lo] (X3: [X | Y] += hi [hi ; lo]^T)
+                            const uint64_t d = umma_desc_sw128(slab + kk * 32);
+                            umma_tf32(d_tmem, d, d, idesc, X3 ? 1u : acc);
                             acc = 1;
                         }
                     }
                     umma_commit(empty0 + 8 * slot); // stage reusable once these MMAs have read it
-                    if (X3) umma_commit(lofree0 + 8 * ls);
-                    ++g;
                     if (++slot == S) {
                         slot = 0;
                         phase ^= 1u;
@@ -264,35 +294,36 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         __syncwarp();
     } else if (X3 && (warp == 2 || warp == 3 || warp >= 8)) {
         // ===================== transform: lo = x - trunc_tf32(x), slab by slab =====================
+        // Same swizzled layout in the twin slab, so the transform is purely elementwise (16 B per lane,
+        // lanes contiguous: conflict-free).
         const int tw = warp < 4 ? warp - 2 : warp - 6; // 0..3
         int slot = 0;
-        uint32_t phase = 0, g = 0;
+        uint32_t phase = 0;
         for (int q = 0; q < nreq; ++q)
-            for (int s = 0; s < spr; ++s, ++g) {
-                const uint32_t ls = g % kTcLoSlots;
-                mbar_wait_backoff(lofree0 + 8 * ls, ((g / kTcLoSlots) & 1u) ^ 1u, 40);
+            for (int s = 0; s < spr; ++s) {
                 mbar_wait_backoff(full0 + 8 * slot, phase, 40);
-                const uint32_t src = smem_u32(ring) + (uint32_t)slot * (uint32_t)stageb;
-                const uint32_t dst = smem_u32(lo_ring) + ls * (uint32_t)rawb;
-                const int n16 = rawb >> 4;
+                const int nk = min(KO, nslab - s * KO);
+                for (int k = 0; k < nk; ++k) {
+                    const uint32_t src = smem_u32(ring) + (uint32_t)slot * (uint32_t)stageb + (uint32_t)k * kSlabStride;
 #pragma unroll 4
-                for (int idx = tw * 32 + lane; idx < n16; idx += NTW * 32) {
-                    float4 x, l;
-                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
-                                 : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w)
-                                 : "r"(src + (uint32_t)idx * 16u));
-                    l.x = x.x - __uint_as_float((__float_as_uint(x.x) + kTcRound) & 0xffffe000u);
-                    l.y = x.y - __uint_as_float((__float_as_uint(x.y) + kTcRound) & 0xffffe000u);
-                    l.z = x.z - __uint_as_float((__float_as_uint(x.z) + kTcRound) & 0xffffe000u);
-                    l.w = x.w - __uint_as_float((__float_as_uint(x.w) + kTcRound) & 0xffffe000u);
-                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (uint32_t)idx * 16u), "f"(l.x), "f"(l.y),
-                                 "f"(l.z), "f"(l.w)
-                                 : "memory");
+                    for (int idx = tw * 32 + lane; idx < kTcSlabBytes / 16; idx += NTW * 32) {
+                        float4 x, l;
+                        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                     : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w)
+                                     : "r"(src + (uint32_t)idx * 16u));
+                        l.x = x.x - __uint_as_float((__float_as_uint(x.x) + kTcRound) & 0xffffe000u);
+                        l.y = x.y - __uint_as_float((__float_as_uint(x.y) + kTcRound) & 0xffffe000u);
+                        l.z = x.z - __uint_as_float((__float_as_uint(x.z) + kTcRound) & 0xffffe000u);
+                        l.w = x.w - __uint_as_float((__float_as_uint(x.w) + kTcRound) & 0xffffe000u);
+                        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(src + (uint32_t)kTcSlabBytes + (uint32_t)idx * 16u),
+                                     "f"(l.x), "f"(l.y), "f"(l.z), "f"(l.w)
+                                     : "memory");
+                    }
                 }
                 // generic-proxy writes must be visible to the tensor core (async proxy) before it is told
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
-                if (lane == 0) mbar_arrive(ready0 + 8 * ls);
+                if (lane == 0) mbar_arrive(ready0 + 8 * slot);
                 if (++slot == S) {
                     slot = 0;
                     phase ^= 1u;
@@ -326,26 +357,40 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                 float row[128];
 #pragma unroll
                 for (int e = 0; e < 128; ++e) row[e] = 0.f;
+                uint32_t z[32];
+#pragma unroll
+                for (int e = 0; e < 32; ++e) z[e] = 0u;
                 for (int ch = 0; ch < nchunk; ++ch, ++tile) {
                     const uint32_t ab = tile & 1u;
                     mbar_wait_backoff(tfull0 + 8 * ab, (tile >> 1) & 1u, 200);
                     tc_fence_after();
-                    const uint32_t row_addr = lane_addr + ab * 128u;
+                    const uint32_t row_addr = lane_addr + ab * 256u; // X half of the [X | Y] accumulator
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         tmem_ld32(row_addr + (uint32_t)(c * 32), v);
+                        tmem_st32(row_addr + (uint32_t)(c * 32), z); // X restarts with the accumulator's next chunk
 #pragma unroll
                         for (int e = 0; e < 32; ++e) row[c * 32 + e] += v[e];
                     }
-                    tc_fence_before();
-                    mbar_arrive(tempty0 + 8 * ab);
+                    if (ch + 1 < nchunk) {
+                        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                        tc_fence_before();
+                        mbar_arrive(tempty0 + 8 * ab);
+                    }
                 }
-                // the last chunk's commit covered every MMA of the request: Y = hi.lo^T is complete too
-                const uint32_t y_addr = lane_addr + 256u + (uint32_t)(q & 1) * 128u;
-                tmem_ld32(y_addr + (uint32_t)(ew * 32), v);
+                // The last chunk's commit covered every MMA of the request, so Y = hi.lo^T is complete too: it sits
+                // in the Y halves of BOTH accumulators (even chunks in one, odd chunks in the other).  The next
+                // request's MMAs wait for Y, so it is drained (and zeroed) before any block-wide step: the diagonal
+                // gives n_i, hence u_i = t_i / n_i, which is all a thread needs to scale ITS row of Y for the
+                // column sums; X + Y stays in row[].
+                const uint32_t last_ab = (tile - 1u) & 1u;
                 float yd = 0.f;
 #pragma unroll
-                for (int e = 0; e < 32; ++e) yd = (lane == e) ? v[e] : yd;
+                for (int h = 0; h < 2; ++h) {
+                    tmem_ld32(lane_addr + (uint32_t)h * 256u + 128u + (uint32_t)(ew * 32), v);
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) yd += (lane == e) ? v[e] : 0.f;
+                }
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
 #pragma unroll
@@ -354,21 +399,31 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                 rn = (act && d > 0.f) ? 1.0f / sqrtf(d) : 0.f;
                 const float ui = t * rn;
                 u_s[i] = ui;
-                epi_sync();
                 // sum_j u_j S_ij = sum_j u_j (X_ij + Y_ij)  [own row]  +  sum_j u_j Y_ji  [column i of u_j-scaled Y]
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
-                    tmem_ld32(y_addr + (uint32_t)(c * 32), v);
+                    float cs = 0.f;
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) {
-                        acc = fmaf(u_s[c * 32 + e], row[c * 32 + e] + v[e], acc);
-                        v[e] *= ui;
+                    for (int h = 0; h < 2; ++h) {
+                        const uint32_t ya = lane_addr + (uint32_t)h * 256u + 128u + (uint32_t)(c * 32);
+                        tmem_ld32(ya, v);
+                        tmem_st32(ya, z);
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) {
+                            row[c * 32 + e] += v[e];
+                            v[e] *= ui;
+                        }
+                        cs += warp_transpose_sum<32>(v, lane); // rows of this warp, column 32c + lane
                     }
-                    col_s[ew * 128 + c * 32 + lane] = warp_transpose_sum<32>(v, lane); // rows of this warp, column 32c + lane
+                    col_s[ew * 128 + c * 32 + lane] = cs;
                 }
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
                 tc_fence_before();
-                mbar_arrive(yempty0 + 8 * (q & 1));
+                mbar_arrive(tempty0 + 8 * last_ab); // the last chunk's X half, zeroed in the loop above
+                mbar_arrive(yempty0);
                 epi_sync();
+#pragma unroll
+                for (int e = 0; e < 128; ++e) acc = fmaf(u_s[e], row[e], acc);
                 acc += (col_s[i] + col_s[128 + i]) + (col_s[256 + i] + col_s[384 + i]);
             } else {
                 const uint32_t ab = tile & 1u;
@@ -463,8 +518,8 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
 }
 
 inline size_t tc_smem_bytes(int ko, int stages, bool x3) {
-    return 1024 + (size_t)(stages + (x3 ? kTcLoSlots : 0)) * ko * kTcSlabBytes + (128 + 128 + 16 + 8 + 2) * 4 +
-           (3 * kTcMaxStages + 6 + kTcLoSlots) * 8 + (x3 ? 4 * 128 * 4 : 0) + 64;
+    return 1024 + (size_t)stages * ko * kTcSlabBytes * (x3 ? 2 : 1) + (128 + 128 + 16 + 8 + 2) * 4 + (3 * kTcMaxStages + 6) * 8 +
+           (x3 ? 4 * 128 * 4 : 0) + 64;
 }
 
 } // namespace lwc
