@@ -12,6 +12,14 @@
 //                                                      tally reads: delta.vote, weight, error.code
 //                                                      (src/score/completions/response.rs:86-107,184-190)
 //   lwc::score::completions::Tally ................... what client.rs:422-463 writes back
+//   lwc::score::completions::response::streaming::
+//        {Delta, Choice, ChatCompletionChunk}::push ... the aggregation of streamed chunks, path fields
+//                                                      only (src/score/completions/response.rs:25-71,
+//                                                      121-173,203-208; chat Delta content concat,
+//                                                      src/chat/completions/response.rs:179-198)
+//   lwc::score::completions::request_from_aggregate,
+//        apply_tally .................................. the gather before and the write-back after the
+//                                                      tally (client.rs:384-420 and 430-456)
 //   lwc::Batcher ..................................... [build-defined] the packer the north star asks
 //                                                      of the Rust host: many threads submit requests,
 //                                                      one worker lays them out [R][N][D] in pinned
@@ -100,6 +108,94 @@ struct Request {
     // candidates' embeddings ordered by Embedding.index; empty -> similarity = identity (the reference)
     const embeddings::response::CreateEmbeddingResponse *embeddings = nullptr;
 };
+
+namespace response::streaming {
+// Streamed chunks are merged into one aggregate before the tally (client.rs:362 `aggregate.push(&chunk)`).
+// Only the fields the scoring path reads or writes are mirrored; the rule is the reference's everywhere:
+// strings concatenate, every other optional keeps its FIRST value, choices merge by `index`.
+struct Delta {
+    std::optional<std::string> content;        // chat Delta.content: push_option_string
+    std::optional<std::vector<double>> vote;   // response.rs:189,203-208: first value wins
+    void push(const Delta &o) {
+        if (o.content) {
+            if (content) *content += *o.content;
+            else content = o.content;
+        }
+        if (!vote) vote = o.vote;
+    }
+};
+struct Choice {
+    Delta delta;
+    std::optional<std::string> finish_reason;
+    uint64_t index = 0;
+    std::optional<double> weight;
+    std::optional<double> confidence;
+    std::optional<error::ResponseError> error;
+    std::optional<std::string> model;
+    std::optional<size_t> model_index;
+    void push(const Choice &o) { // response.rs:121-173
+        delta.push(o.delta);
+        if (!finish_reason) finish_reason = o.finish_reason;
+        if (!weight) weight = o.weight;
+        if (!confidence) confidence = o.confidence;
+        if (!error) error = o.error;
+        if (!model) model = o.model;
+        if (!model_index) model_index = o.model_index;
+    }
+};
+struct ChatCompletionChunk {
+    std::string id;
+    std::vector<Choice> choices;
+    uint64_t created = 0;
+    std::string model;
+    void push(const ChatCompletionChunk &o) { // response.rs:25-71: choices by index, unknown index appended
+        for (const Choice &oc : o.choices) {
+            auto it = std::find_if(choices.begin(), choices.end(), [&](const Choice &c) { return c.index == oc.index; });
+            if (it != choices.end()) it->push(oc);
+            else choices.push_back(oc);
+        }
+    }
+};
+} // namespace response::streaming
+
+// client.rs:384-420: the voters are the aggregate's choices AFTER the first `n_choices` (the request's own
+// candidates come first); each contributes delta.vote, weight and error.code.
+inline Request request_from_aggregate(const response::streaming::ChatCompletionChunk &aggregate, int32_t n_choices,
+                                      const embeddings::response::CreateEmbeddingResponse *embeddings = nullptr) {
+    Request rq;
+    rq.n_choices = n_choices;
+    rq.embeddings = embeddings;
+    for (size_t k = (size_t)n_choices; k < aggregate.choices.size(); ++k) {
+        const auto &c = aggregate.choices[k];
+        VoterChoice v;
+        v.vote = c.delta.vote;
+        v.weight = c.weight;
+        if (c.error) v.error_code = c.error->code;
+        rq.voters.push_back(std::move(v));
+    }
+    return rq;
+}
+
+// client.rs:430-456: candidates (index < n_choices) receive weight and confidence; voters receive their
+// agreement with the consensus; then delta, finish_reason and error are cleared on every choice.
+inline void apply_tally(response::streaming::ChatCompletionChunk &aggregate, const Tally &tally, int32_t n_choices) {
+    size_t voter = 0;
+    for (size_t k = 0; k < aggregate.choices.size(); ++k) {
+        auto &c = aggregate.choices[k];
+        if (c.index < (uint64_t)n_choices) {
+            c.weight = tally.weight[c.index];
+            c.confidence = tally.confidence[c.index];
+        }
+        if (k >= (size_t)n_choices) { // voters are positional (skip(n)), like the gather above
+            if (c.index >= (uint64_t)n_choices && voter < tally.voter_confidence.size() && tally.voter_confidence[voter])
+                c.confidence = c.confidence.value_or(0.0) + *tally.voter_confidence[voter];
+            ++voter;
+        }
+        c.delta = response::streaming::Delta{};
+        c.finish_reason.reset();
+        c.error.reset();
+    }
+}
 
 } // namespace score::completions
 

@@ -34,6 +34,73 @@ static int cpu_checks() {
     v[1].error_code.reset(); // a voter without an error: not an all-failed request
     REQUIRE(!merge_error_codes(v).has_value());
     REQUIRE(merge_error_codes({}).value() == 500); // AllVotesFailed(None) -> 500 (error.rs:41)
+
+    // streamed-chunk aggregation (response.rs:25-71,121-173,203-208) and the gather / write-back around the
+    // tally (client.rs:384-456)
+    namespace st = score::completions::response::streaming;
+    st::ChatCompletionChunk agg;
+    agg.id = "rsp";
+    for (uint64_t i = 0; i < 2; ++i) { // the request's two candidate choices come first
+        st::Choice c;
+        c.index = i;
+        c.delta.content = i == 0 ? "yes" : "no";
+        agg.choices.push_back(c);
+    }
+    st::ChatCompletionChunk a, b, c3;
+    {
+        st::Choice c;
+        c.index = 2; // voter 0, first piece
+        c.delta.content = "{\"resp";
+        c.model = "llm-a";
+        c.model_index = 0;
+        a.choices.push_back(c);
+        c = st::Choice{};
+        c.index = 2; // voter 0, last piece: vote and weight arrive at the end
+        c.delta.content = "onse\": 1}";
+        c.delta.vote = std::vector<double>{0.25, 0.75};
+        c.weight = 2.0;
+        c.model = "ignored: first value wins";
+        c.finish_reason = "stop";
+        b.choices.push_back(c);
+        c = st::Choice{};
+        c.index = 3; // voter 1 failed
+        c.error = error::ResponseError(429, "rate limited");
+        c.weight = 1.0;
+        c3.choices.push_back(c);
+    }
+    agg.push(a);
+    agg.push(b);
+    agg.push(c3);
+    REQUIRE(agg.choices.size() == 4);
+    REQUIRE(*agg.choices[2].delta.content == "{\"response\": 1}");
+    REQUIRE(*agg.choices[2].model == "llm-a" && *agg.choices[2].model_index == 0);
+    REQUIRE(*agg.choices[2].finish_reason == "stop");
+    st::ChatCompletionChunk late;
+    {
+        st::Choice c;
+        c.index = 2;
+        c.delta.vote = std::vector<double>{1.0, 0.0}; // a second vote must not replace the first
+        c.weight = 9.0;
+        late.choices.push_back(c);
+    }
+    agg.push(late);
+    REQUIRE((*agg.choices[2].delta.vote)[1] == 0.75 && *agg.choices[2].weight == 2.0);
+    const Request rq = score::completions::request_from_aggregate(agg, 2);
+    REQUIRE(rq.n_choices == 2 && rq.voters.size() == 2);
+    REQUIRE(rq.voters[0].vote.has_value() && (*rq.voters[0].vote)[0] == 0.25 && *rq.voters[0].weight == 2.0);
+    REQUIRE(!rq.voters[0].error_code.has_value());
+    REQUIRE(!rq.voters[1].vote.has_value() && *rq.voters[1].error_code == 429);
+    REQUIRE(!merge_error_codes(rq.voters).has_value()); // one voter succeeded
+    Tally t; // what the reference arithmetic gives for this aggregate: t = 2 * (0.25, 0.75)
+    t.weight = {0.5, 1.5};
+    t.confidence = {0.25, 0.75};
+    t.voter_confidence = {0.25 * 0.25 + 0.75 * 0.75, std::nullopt};
+    score::completions::apply_tally(agg, t, 2);
+    REQUIRE(*agg.choices[0].weight == 0.5 && *agg.choices[1].confidence == 0.75);
+    REQUIRE(std::fabs(*agg.choices[2].confidence - 0.625) < 1e-12);
+    REQUIRE(!agg.choices[3].confidence.has_value()); // no vote: untouched (client.rs:440)
+    for (const auto &ch : agg.choices)
+        REQUIRE(!ch.delta.content && !ch.delta.vote && !ch.finish_reason && !ch.error); // client.rs:451-454
     return 0;
 }
 
