@@ -6,6 +6,9 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
+#include <vector>
+#include <algorithm>
 
 #include "lwc_internal.hpp"
 #include "score_generic.cuh"
@@ -636,7 +639,26 @@ int32_t lwc_vote_from_logprobs(lwc_ctx *ctx, int32_t n_rows, int32_t n_top, int3
 
 int32_t lwc_stage_f64(lwc_ctx *ctx, const double *src, size_t n, float *dst) {
     if (n && (!src || !dst)) return fail(ctx, LWC_ERR_INVALID, "lwc_stage_f64: NULL argument");
-    for (size_t i = 0; i < n; ++i) dst[i] = static_cast<float>(src[i]);
+    // one embedding (a few thousand values) converts inline; a whole batch is split over host threads so the
+    // conversion keeps up with the PCIe copy that follows it
+    const size_t kPerThread = (size_t)1 << 20;
+    unsigned nt = (unsigned)((n + kPerThread - 1) / kPerThread);
+    const unsigned hw = std::thread::hardware_concurrency();
+    if (nt > (hw ? hw : 1u)) nt = hw ? hw : 1u;
+    if (nt > 16u) nt = 16u;
+    auto convert = [src, dst](size_t a, size_t b) {
+        for (size_t i = a; i < b; ++i) dst[i] = static_cast<float>(src[i]);
+    };
+    if (nt <= 1) {
+        convert(0, n);
+        return LWC_OK;
+    }
+    std::vector<std::thread> pool;
+    pool.reserve(nt - 1);
+    const size_t per = (n + nt - 1) / nt;
+    for (unsigned t = 1; t < nt; ++t) pool.emplace_back(convert, std::min(n, t * per), std::min(n, (t + 1) * per));
+    convert(0, std::min(n, per));
+    for (auto &th : pool) th.join();
     return LWC_OK;
 }
 

@@ -82,3 +82,16 @@ def test_rust_sys_crate_declares_every_c_symbol():
     rs = open(os.path.join(ROOT, "rust", "lwc-b200-sys", "src", "lib.rs")).read()
     for name in declared_symbols():
         assert re.search(r"\bfn %s\b" % name, rs), f"{name} missing from rust/lwc-b200-sys/src/lib.rs"
+
+
+def test_stage_f64_is_a_host_function_and_rounds_like_a_cast(lwc):
+    """lwc_stage_f64 needs no device (NULL context is fine): small arrays convert inline, large ones on threads."""
+    L = lwc.load_library()
+    rng = np.random.default_rng(9)
+    for n in (0, 1, 1536, 5_000_001):
+        src = rng.standard_normal(n) * 10.0 ** rng.integers(-20, 20, n)
+        dst = np.full(n + 1, 7.0, np.float32)
+        rc = L.lwc_stage_f64(None, ctypes.c_void_p(src.ctypes.data), n, ctypes.c_void_p(dst.ctypes.data))
+        assert rc == 0
+        assert (dst[:n] == src.astype(np.float32)).all() and dst[n] == 7.0
+    assert L.lwc_stage_f64(None, None, 4, None) == 400
