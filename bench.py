@@ -35,7 +35,7 @@ for _p in (ROOT, os.path.join(ROOT, "llm-weighted-consensus_b200")):
 
 import numpy as np  # noqa: E402
 
-METRIC = "scored_requests_per_sec"
+METRIC = "scored requests/sec (16×1536 emb)"  # BASELINE.json's metric, without its "at 1/2/4/8 B200; % of roofline" tail
 UNIT = "requests/s"
 WORKLOAD = "cfg2"
 
@@ -398,7 +398,7 @@ def run_other_workload(args, torch, lwc_b200, synth, local_rank, rank=0, world=1
     achieved = nbytes / (ms * 1e-3) / 1e9
     if rank == 0:
         print(json.dumps({
-            "metric": METRIC, "value": R_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "metric": f"scored requests/sec ({N}×{D} emb)", "value": R_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "scaling": "strong", "dtype": "f32",
             "data": "synthetic (generated in HBM)",
             "config": {"workload": f"{args.workload}: {R_total} requests x {N} candidates x {D}-dim fp32, {M} voters"
