@@ -117,19 +117,28 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.samples)}
 
 
+def host_cores():
+    """Threads the CPU arm uses: every core this process may run on.  (torchrun exports OMP_NUM_THREADS=1 to
+    its workers; the reference arm is one process that owns the box, so it does not follow that.)"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_baseline(E, V, w, budget_s=10.0):
     """Reference-typed CPU port on all host cores, bounded sample of the same workload."""
     import oracle
 
     R = V.shape[0]
-    cores = oracle.num_threads()
+    cores = host_cores()
     probe = min(R, 256)
-    t = oracle.score_port(E[:probe], V[:probe], w[:probe], oracle.SIM_COSINE)["seconds"]
+    t = oracle.score_port(E[:probe], V[:probe], w[:probe], oracle.SIM_COSINE, nthreads=cores)["seconds"]
     per_req = max(t / probe, 1e-9)
     n = int(min(R, max(probe, budget_s / per_req)))
     reps, total_req, total_s = 0, 0, 0.0
     while total_s < budget_s and reps < 4096:
-        total_s += oracle.score_port(E[:n], V[:n], w[:n], oracle.SIM_COSINE)["seconds"]
+        total_s += oracle.score_port(E[:n], V[:n], w[:n], oracle.SIM_COSINE, nthreads=cores)["seconds"]
         total_req += n
         reps += 1
     return {"value": total_req / total_s, "unit": UNIT, "cores": cores, "kind": "port",
@@ -148,10 +157,10 @@ def run_reference(args):
     R, N, D, M = synth.CONFIGS[WORKLOAD]
     sample = min(R, 1024)
     E, V, w, _ = synth.make_batch(sample, N, D, M)
-    cores = oracle.num_threads()
+    cores = host_cores()
     for _ in range(args.warmup):
-        oracle.score_port(E, V, w, oracle.SIM_COSINE)
-    secs = [oracle.score_port(E, V, w, oracle.SIM_COSINE)["seconds"] for _ in range(args.steps)]
+        oracle.score_port(E, V, w, oracle.SIM_COSINE, nthreads=cores)
+    secs = [oracle.score_port(E, V, w, oracle.SIM_COSINE, nthreads=cores)["seconds"] for _ in range(args.steps)]
     total = float(np.sum(secs))
     value = sample * args.steps / total
     line = {

@@ -22,7 +22,8 @@ def run_bench(*flags, env=None):
 
 
 def test_reference_arm_prints_one_contract_line():
-    out = run_bench("--impl", "reference", "--steps", "1", "--warmup", "0", env={"OMP_NUM_THREADS": "4"})
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: the reference arm must still use the whole box
+    out = run_bench("--impl", "reference", "--steps", "1", "--warmup", "0", env={"OMP_NUM_THREADS": "1"})
     assert out.returncode == 0, out.stderr[-2000:]
     lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
     assert len(lines) == 1
@@ -32,6 +33,7 @@ def test_reference_arm_prints_one_contract_line():
     assert base["metric"].startswith(d["metric"]) and d["unit"] == "requests/s"
     assert d["value"] > 0 and d["gpu_launches"] == 0
     assert d["cpu_baseline"]["kind"] in ("port", "reference") and d["cpu_baseline"]["value"] == d["value"]
+    assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert "workload" in d["config"] and "model" not in d["config"]
 
