@@ -242,15 +242,20 @@ int32_t lwc_pool_p2p_attach(lwc_ctx *ctx, const void *all_handles /* nranks * 12
  * lwc_table_load: copies a table of `rows` past prompts to the GPU and keeps it resident in the
  *   context: T [rows][D] prompt embeddings, Q [rows][M] each LLM's recorded quality on that prompt
  *   (>= 0; e.g. the confidence it gave the winning choice).  Replaces a previously loaded table.
- * lwc_table_weights: for each of n_prompts new prompt embeddings q [n_prompts][D] (host memory), finds
+ * lwc_table_weights: for each of n_prompts new prompt embeddings q [n_prompts][D], finds
  *   the `top` most cosine-similar table rows (ties -> lowest row) and writes
  *     weights[p][m] = clamp(base[m] * rho_m / mean_m'(rho_m'), minw[m], maxw[m]),
  *     rho_m = sum_k max(sim_k, 0) Q[idx_k][m] / sum_k max(sim_k, 0);   base[m] when no neighbour has sim > 0.
  *   400 unless 0 < minw <= base <= maxw for every LLM (the reference's validate()) and 1 <= top <= 64.
- *   top_idx / top_sim ([n_prompts][top], -1 / 0 past the table's size) may be NULL.  Blocking. */
+ *   top_idx / top_sim ([n_prompts][top], -1 / 0 past the table's size) may be NULL.
+ *   memory = LWC_MEM_HOST: q, weights, top_idx, top_sim are host pointers and the call blocks.
+ *   memory = LWC_MEM_DEVICE: they are device pointers and the call is asynchronous on the context's stream
+ *   (lwc_ctx_stream): `weights` can be passed as `w` (w_per_request = 1) to an lwc_score_batch call on
+ *   that stream without touching the host.  base / minw / maxw are host arrays either way. */
 int32_t lwc_table_load(lwc_ctx *ctx, const float *T, const float *Q, int64_t rows, int32_t D, int32_t M);
 int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32_t top, const float *base,
-                          const float *minw, const float *maxw, float *weights, int32_t *top_idx, float *top_sim);
+                          const float *minw, const float *maxw, float *weights, int32_t *top_idx, float *top_sim,
+                          int32_t memory);
 
 #ifdef __cplusplus
 }

@@ -48,11 +48,15 @@ int32_t lwc_table_load(lwc_ctx *ctx, const float *T, const float *Q, int64_t row
 }
 
 int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32_t top, const float *base,
-                          const float *minw, const float *maxw, float *weights, int32_t *top_idx, float *top_sim) {
+                          const float *minw, const float *maxw, float *weights, int32_t *top_idx, float *top_sim,
+                          int32_t memory) {
     if (!ctx) return LWC_ERR_INVALID;
     std::lock_guard<std::mutex> lk(ctx->mu);
     if (ctx->table_rows == 0) return fail(ctx, LWC_ERR_INVALID, "lwc_table_weights: no table loaded (lwc_table_load)");
     // `top` >= 1 as WeightTrainingTable::validate demands (src/score/model/mod.rs:292-297)
+    if (memory != LWC_MEM_HOST && memory != LWC_MEM_DEVICE)
+        return fail(ctx, LWC_ERR_INVALID, "lwc_table_weights: memory must be LWC_MEM_HOST or LWC_MEM_DEVICE");
+    const bool dev = memory == LWC_MEM_DEVICE;
     if (!q || !base || !minw || !maxw || !weights || n_prompts < 0 || top < 1 || top > lwc::kTableMaxTop)
         return fail(ctx, LWC_ERR_INVALID, "lwc_table_weights: invalid argument (prompts=%d top=%d, top must be 1..%d)",
                     n_prompts, top, lwc::kTableMaxTop);
@@ -96,9 +100,13 @@ int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32
     if (smem > 48 * 1024) CUDA_TRY(ctx, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     for (int b0 = 0; b0 < n_prompts; b0 += QB) {
         const int nq = n_prompts - b0 < QB ? n_prompts - b0 : QB;
-        CUDA_TRY(ctx, cudaMemcpyAsync(sb + o_q, q + (size_t)b0 * D, (size_t)nq * D * 4, cudaMemcpyHostToDevice, st));
+        if (!dev) CUDA_TRY(ctx, cudaMemcpyAsync(sb + o_q, q + (size_t)b0 * D, (size_t)nq * D * 4, cudaMemcpyHostToDevice, st));
         const float *Td = static_cast<const float *>(ctx->table_buf[0]), *rn = static_cast<const float *>(ctx->table_buf[1]);
-        const float *qd = reinterpret_cast<const float *>(sb + o_q);
+        const float *qd = dev ? q + (size_t)b0 * D : reinterpret_cast<const float *>(sb + o_q);
+        // device memory: results go straight to the caller's buffers; host memory: through the pass's scratch
+        int32_t *idx_o = dev && top_idx ? top_idx + (size_t)b0 * top : reinterpret_cast<int32_t *>(sb + o_idx);
+        float *sim_o = dev && top_sim ? top_sim + (size_t)b0 * top : reinterpret_cast<float *>(sb + o_sim);
+        float *w_o = dev ? weights + (size_t)b0 * M : reinterpret_cast<float *>(sb + o_w);
         float *scd = reinterpret_cast<float *>(s3);
         if (RS) {
             const long long groups = (Tn + RS - 1) / RS;
@@ -123,8 +131,8 @@ int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32
                 const bool last = ch == 1;
                 float *ov = reinterpret_cast<float *>(s3 + o_cv + (size_t)(level & 1) * 2 * cand_bytes);
                 int32_t *oi = reinterpret_cast<int32_t *>(s3 + o_cv + (size_t)(level & 1) * 2 * cand_bytes + cand_bytes);
-                int32_t *fi = last ? reinterpret_cast<int32_t *>(sb + o_idx) : nullptr;
-                float *fs = last ? reinterpret_cast<float *>(sb + o_sim) : nullptr;
+                int32_t *fi = last ? idx_o : nullptr;
+                float *fs = last ? sim_o : nullptr;
                 const dim3 grid((unsigned)ch, nq);
                 if (ii) lwc::table_topk_kernel<true><<<grid, lwc::kTopkThreads, 0, st>>>(iv, ii, n, top, ov, oi, fi, fs);
                 else lwc::table_topk_kernel<false><<<grid, lwc::kTopkThreads, 0, st>>>(iv, ii, n, top, ov, oi, fi, fs);
@@ -134,17 +142,18 @@ int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32
             }
         }
         lwc::table_weights_kernel<<<(nq + 3) / 4, 128, 0, st>>>(
-            reinterpret_cast<const int32_t *>(sb + o_idx), reinterpret_cast<const float *>(sb + o_sim),
-            static_cast<const float *>(ctx->table_buf[2]), reinterpret_cast<const float *>(sb + o_lim),
+            idx_o, sim_o, static_cast<const float *>(ctx->table_buf[2]), reinterpret_cast<const float *>(sb + o_lim),
             reinterpret_cast<const float *>(sb + o_lim + (size_t)M * 4), reinterpret_cast<const float *>(sb + o_lim + (size_t)2 * M * 4),
-            reinterpret_cast<float *>(sb + o_w), nq, top, M);
+            w_o, nq, top, M);
         CUDA_TRY(ctx, cudaGetLastError());
         ctx->launches += 2;
-        CUDA_TRY(ctx, cudaMemcpyAsync(weights + (size_t)b0 * M, sb + o_w, (size_t)nq * M * 4, cudaMemcpyDeviceToHost, st));
-        if (top_idx) CUDA_TRY(ctx, cudaMemcpyAsync(top_idx + (size_t)b0 * top, sb + o_idx, (size_t)nq * top * 4, cudaMemcpyDeviceToHost, st));
-        if (top_sim) CUDA_TRY(ctx, cudaMemcpyAsync(top_sim + (size_t)b0 * top, sb + o_sim, (size_t)nq * top * 4, cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(ctx, cudaStreamSynchronize(st)); // the pass's scratch is reused by the next one
+        if (!dev) { // stream order protects the scratch: these copies precede the next pass's upload and kernels
+            CUDA_TRY(ctx, cudaMemcpyAsync(weights + (size_t)b0 * M, w_o, (size_t)nq * M * 4, cudaMemcpyDeviceToHost, st));
+            if (top_idx) CUDA_TRY(ctx, cudaMemcpyAsync(top_idx + (size_t)b0 * top, idx_o, (size_t)nq * top * 4, cudaMemcpyDeviceToHost, st));
+            if (top_sim) CUDA_TRY(ctx, cudaMemcpyAsync(top_sim + (size_t)b0 * top, sim_o, (size_t)nq * top * 4, cudaMemcpyDeviceToHost, st));
+        }
     }
+    if (!dev) CUDA_TRY(ctx, cudaStreamSynchronize(st)); // host results are valid on return; device results in stream order
     return LWC_OK;
 }
 

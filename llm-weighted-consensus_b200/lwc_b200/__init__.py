@@ -100,7 +100,7 @@ def load_library():
     L.lwc_comm_destroy.restype = i32
     L.lwc_table_load.argtypes = [vp, vp, vp, ctypes.c_int64, i32, i32]
     L.lwc_table_load.restype = i32
-    L.lwc_table_weights.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, vp, vp]
+    L.lwc_table_weights.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, i32]
     L.lwc_table_weights.restype = i32
     L.lwc_stage_f64.argtypes = [vp, vp, ctypes.c_size_t, vp]
     L.lwc_stage_f64.restype = i32
@@ -343,8 +343,15 @@ class Context:
         idx = np.zeros((B, max(top, 1)), np.int32)
         sim = np.zeros((B, max(top, 1)), np.float32)
         self._check(self.lib.lwc_table_weights(self.handle, _np_ptr(q), B, top, _np_ptr(base), _np_ptr(minw),
-                                               _np_ptr(maxw), _np_ptr(weights), _np_ptr(idx), _np_ptr(sim)))
+                                               _np_ptr(maxw), _np_ptr(weights), _np_ptr(idx), _np_ptr(sim), MEM_HOST))
         return weights, idx, sim
+
+    def table_weights_device(self, q_ptr, n_prompts, top, base, minw, maxw, weights_ptr, idx_ptr=None, sim_ptr=None):
+        """lwc_table_weights with device pointers (ints): asynchronous on the context's stream."""
+        base, minw, maxw = (np.ascontiguousarray(a, dtype=np.float32) for a in (base, minw, maxw))
+        vp = lambda x: None if x is None else ctypes.c_void_p(x)
+        self._check(self.lib.lwc_table_weights(self.handle, vp(q_ptr), n_prompts, top, _np_ptr(base), _np_ptr(minw),
+                                               _np_ptr(maxw), vp(weights_ptr), vp(idx_ptr), vp(sim_ptr), MEM_DEVICE))
 
     def stage_f64(self, src, dst):
         src = np.ascontiguousarray(src, dtype=np.float64)

@@ -125,5 +125,6 @@ extern "C" {
         weights: *mut f32,
         top_idx: *mut i32,
         top_sim: *mut f32,
+        memory: i32,
     ) -> i32;
 }

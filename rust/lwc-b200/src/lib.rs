@@ -126,7 +126,7 @@ impl Context {
         let mut w = vec![0f32; base.len()];
         let rc = unsafe {
             sys::lwc_table_weights(self.0, prompt.as_ptr(), 1, top as i32, base.as_ptr(), min.as_ptr(), max.as_ptr(),
-                w.as_mut_ptr(), std::ptr::null_mut(), std::ptr::null_mut())
+                w.as_mut_ptr(), std::ptr::null_mut(), std::ptr::null_mut(), sys::LWC_MEM_HOST)
         };
         if rc != 0 {
             return Err(response_error(rc, self.0));

@@ -145,3 +145,36 @@ def test_table_topk_tree_three_levels_and_ties():
         ctx.table_load(Tt[:5], np.ones((5, 2), np.float32))
         _, idx, sim = ctx.table_weights(np.ones((1, 8), np.float32), 8, one, one, one)
         assert (idx[0] == [0, 1, 2, 3, 4, -1, -1, -1]).all() and (sim[0, 5:] == 0).all()
+
+
+@pytest.mark.gpu
+def test_table_weights_device_memory_feeds_score_batch(oracle):
+    """Device pointers in, device weights out, asynchronous on the context's stream: the weights go straight into a
+    scoring call on that stream, and equal what the host-memory call returns bit for bit."""
+    import torch
+    import lwc_b200
+    from lwc_b200 import synth
+    R, N, D, M, top = 19, 16, 256, 4, 5
+    T, Q, q, base, minw, maxw = make_table(21, 3000, D, M, R)
+    E, V, _, _ = synth.make_batch(R, N, D, M)
+    with lwc_b200.Context(0) as ctx:
+        ctx.table_load(T, Q)
+        w_host, idx_host, sim_host = ctx.table_weights(q, top, base, minw, maxw)
+        st = torch.cuda.ExternalStream(ctx.stream())
+        with torch.cuda.stream(st):
+            dq = torch.from_numpy(q).cuda()
+            dE, dV = torch.from_numpy(E).cuda(), torch.from_numpy(V).cuda()
+            dw = torch.empty((R, M), dtype=torch.float32, device="cuda")
+            didx = torch.empty((R, top), dtype=torch.int32, device="cuda")
+            dconf = torch.empty((R, N), dtype=torch.float32, device="cuda")
+            dwin = torch.empty((R,), dtype=torch.int32, device="cuda")
+            torch.cuda.synchronize()
+            ctx.table_weights_device(dq.data_ptr(), R, top, base, minw, maxw, dw.data_ptr(), didx.data_ptr(), None)
+            desc = lwc_b200.BatchDesc(R, N, D, M, lwc_b200.SIM_COSINE, lwc_b200.PREC_FP32, lwc_b200.MEM_DEVICE, 1)
+            ctx.score_raw(desc, dE.data_ptr(), dV.data_ptr(), dw.data_ptr(), dconf.data_ptr(), None, None, dwin.data_ptr(),
+                          None)
+            ctx.synchronize()
+        assert (dw.cpu().numpy() == w_host).all() and (didx.cpu().numpy() == idx_host).all()
+        ref = oracle.score_f64(E, V, w_host, oracle.SIM_COSINE)
+        np.testing.assert_allclose(dconf.cpu().numpy(), ref["conf"], rtol=1e-5, atol=1e-7)
+        assert ctx.lib.lwc_table_weights(ctx.handle, None, 1, 1, None, None, None, None, None, None, 7) == 400
