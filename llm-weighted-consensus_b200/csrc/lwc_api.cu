@@ -116,7 +116,7 @@ Plan plan_for(const lwc_batch_desc &d, const void *E) {
 template <int NP>
 cudaError_t launch_generic(const lwc::ScoreParams &p, cudaStream_t st) {
     using C = lwc::GenericCfg<NP>;
-    static bool configured[64] = {false};
+    static std::atomic<bool> configured[64]; // zero-initialised; set once per device (contexts on other threads may race here)
     int dev = 0;
     cudaGetDevice(&dev);
     if (!configured[dev & 63]) {
@@ -132,7 +132,7 @@ cudaError_t launch_generic(const lwc::ScoreParams &p, cudaStream_t st) {
 template <int NT, bool X3, int KW, int U>
 cudaError_t launch_small_one(const lwc::ScoreParams &p, cudaStream_t st) {
     using C = lwc::SmallCfg<NT, X3, KW, U>;
-    static bool configured[64] = {false};
+    static std::atomic<bool> configured[64]; // zero-initialised; set once per device (contexts on other threads may race here)
     int dev = 0;
     cudaGetDevice(&dev);
     if (!configured[dev & 63]) {
@@ -184,7 +184,7 @@ cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) 
     while (geo.stages > 1 && lwc::tc_smem_bytes(geo.ko, geo.stages, X3) > (size_t)ctx->max_smem_optin) --geo.stages;
     if (ctx->tc_stages > 0 && ctx->tc_stages < geo.stages) geo.stages = ctx->tc_stages;
     if (lwc::tc_smem_bytes(geo.ko, geo.stages, X3) > (size_t)ctx->max_smem_optin) return cudaErrorInvalidConfiguration;
-    static bool configured[64] = {false};
+    static std::atomic<bool> configured[64]; // zero-initialised; set once per device (contexts on other threads may race here)
     if (!configured[ctx->device & 63]) {
         cudaError_t e = cudaFuncSetAttribute(lwc::score_tc_kernel<X3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              ctx->max_smem_optin);
@@ -216,7 +216,7 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
     if (geo.stages > C::MAXS) geo.stages = C::MAXS;
     if (ctx->stream_slots >= 1 && ctx->stream_slots < geo.stages) geo.stages = ctx->stream_slots;
     if (geo.stages < 1) return cudaErrorInvalidConfiguration;
-    static bool configured[64] = {false};
+    static std::atomic<bool> configured[64]; // zero-initialised; set once per device (contexts on other threads may race here)
     if (!configured[ctx->device & 63]) {
         cudaError_t e = cudaFuncSetAttribute(lwc::score_stream_kernel<NT, X3, NCW, NF>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);

@@ -7,6 +7,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <atomic>
 #include <mutex>
 #include <string>
 

@@ -142,7 +142,7 @@ int pool_run(lwc_ctx *ctx, const PoolScratch &sc, const float *dE, const float *
         if (!make_tensor_map_bf16_2d(&tmA, sc.ehat_all, n_total, D, lwc::kPoolTM) ||
             !make_tensor_map_bf16_2d(&tmB, sc.ehat_all, n_total, D, lwc::kPoolTN))
             return fail(ctx, LWC_ERR_INTERNAL, "cuTensorMapEncodeTiled failed for the pool operand (D=%d)", D);
-        static bool configured[64] = {false};
+        static std::atomic<bool> configured[64]; // zero-initialised; set once per device (contexts on other threads may race here)
         if (!configured[ctx->device & 63]) {
             CUDA_TRY(ctx, cudaFuncSetAttribute(lwc::pool_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                (int)lwc::pool_gemm_smem_bytes()));

@@ -29,6 +29,7 @@ int32_t lwc_table_load(lwc_ctx *ctx, const float *T, const float *Q, int64_t row
     if (!T || !Q || rows < 1 || rows > 0x7fffffffLL || D < 1 || M < 1 || M > LWC_MAX_VOTERS)
         return fail(ctx, LWC_ERR_INVALID, "lwc_table_load: invalid table (rows=%lld D=%d M=%d)", (long long)rows, D, M);
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    ctx->table_rows = 0; // no table until this load has succeeded
     int rc;
     if ((rc = table_ensure(ctx, 0, (size_t)rows * D * 4))) return rc;
     if ((rc = table_ensure(ctx, 1, (size_t)rows * 4))) return rc;
