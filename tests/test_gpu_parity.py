@@ -265,11 +265,37 @@ def test_cfg4_shape_slice(ctx, lwc, oracle):
     _, N, D, M = synth.CONFIGS["cfg4"]
     R = 24
     E, V, w, kinds = synth.make_batch(R, N, D, M, seed=4)
-    assert ctx.kernel_for(R, N, D, M) == "tc128_tf32x3"  # fp32-grade on tcgen05: three MMAs per K step
+    assert ctx.kernel_for(R, N, D, M) == "tc128_tf32x3"  # fp32-grade on tcgen05: tf32 product + bf16 correction product
     got = ctx.score_batch(E, V, w)
     properties_hold(got, V)
     want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
     assert compare(got, want, V) == 1.0
+
+
+@pytest.mark.parametrize("D", [3072, 8192])
+@pytest.mark.parametrize("positive", [False, True], ids=["mixed_sign", "all_positive"])
+def test_large_pool_fp32_grade_error_margin(ctx, lwc, oracle, D, positive):
+    """The fp32-grade tensor route must hold the 1e-5 bar with room to spare, also on the input that is worst for it:
+    all-positive embeddings, where every partial sum has the same sign and the tensor core's truncating accumulator
+    drifts the most (the reason its accumulation is chunked), and at a D well above the benchmark's."""
+    rng = np.random.default_rng(D + positive)
+    R, N, M = 6, 128, 8
+    E = rng.standard_normal((R, N, D)).astype(np.float32)
+    if positive:
+        E = np.abs(E)
+    V = rng.random((R, M, N)).astype(np.float32) ** 4
+    V /= V.sum(axis=2, keepdims=True)
+    w = (rng.random((R, M)) + 0.5).astype(np.float32)
+    assert ctx.kernel_for(R, N, D, M) == "tc128_tf32x3"
+    got = ctx.score_batch(E, V, w)
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    # fraction of the stated tolerance (1e-5 relative + 1e-7 absolute, parity_util) that is used up
+    used = np.abs(got["conf"] - want["conf"]) / (CONF_RTOL * np.abs(want["conf"]) + CONF_ATOL)
+    scale = np.abs(want["cw"]).max(axis=1, keepdims=True)
+    usedw = np.abs(got["cw"] - want["cw"]) / scale / (CONF_RTOL * np.abs(want["cw"]) / scale + 1e-6)
+    print(f"fp32-grade tc route, D={D}, positive={positive}: tolerance used, conf {used.max():.3f}, cw {usedw.max():.3f}")
+    assert used.max() < 0.5 and usedw.max() < 0.5
+    assert (got["winner"] == want["winner"]).all()
 
 
 # ------------------------------------------------------------------ argument errors
