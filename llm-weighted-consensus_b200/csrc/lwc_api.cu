@@ -177,10 +177,9 @@ bool make_tensor_map_tc(CUtensorMap *tm, const float *E, int R, int N, int D, in
 template <bool X3>
 cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
     lwc::TcGeom geo;
-    geo.ko = ctx->tc_ko > 0 ? ctx->tc_ko : 4; // 64 KB boxes (profiles/r1_tma_probe2.txt); the fp32-grade route adds 32 KB of bf16 per stage
+    geo.ko = ctx->tc_ko > 0 ? ctx->tc_ko : (X3 ? 2 : 4); // 64 KB per stage either way (profiles/r1_tma_probe2.txt)
     const int nslab = p.D / 32;
     if (geo.ko > nslab) geo.ko = nslab;
-    if (X3 && (geo.ko & 1)) ++geo.ko; // a bf16 operand slab spans two raw slabs (a box past D is zero-filled)
     geo.stages = lwc::kTcMaxStages;
     while (geo.stages > 1 && lwc::tc_smem_bytes(geo.ko, geo.stages, X3) > (size_t)ctx->max_smem_optin) --geo.stages;
     if (ctx->tc_stages > 0 && ctx->tc_stages < geo.stages) geo.stages = ctx->tc_stages;
@@ -193,7 +192,8 @@ cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) 
         configured[ctx->device & 63] = true;
     }
     CUtensorMap tm;
-    if (!make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, geo.ko)) return cudaErrorInvalidValue;
+    // fp32-grade route: one box per slab (the slabs of a stage are interleaved with their remainder slabs)
+    if (!make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, X3 ? 1 : geo.ko)) return cudaErrorInvalidValue;
     const int grid = p.R < ctx->sm_count ? p.R : ctx->sm_count;
     lwc::score_tc_kernel<X3><<<grid, X3 ? lwc::kTcThreadsX3 : lwc::kTcThreads, lwc::tc_smem_bytes(geo.ko, geo.stages, X3), st>>>(
         tm, p, geo);

@@ -22,50 +22,47 @@
 //
 // X3 = false: inputs are read by the tensor core as TF32 (the low 13 mantissa bits of each fp32 are
 // ignored) -- the `precision = LWC_PREC_TF32` route with the stated 2e-3 confidence tolerance.
-// X3 = true: fp32-grade result.  With hi = trunc_tf32(x) (what the tensor core sees of an fp32 operand --
-// measured: it truncates) and lo = x - hi:  S = X + Y + Y^T,  X = hi.hi^T,  Y = lo.hi^T  (lo.lo^T < 2^-20 is
-// dropped).  The third product of the classic 3xTF32 scheme is the transpose of the second, so it is never
-// computed: the epilogue folds Y in twice, once along its row and once, through a warp transpose-sum, along its
-// column.  X runs as kind::tf32 MMAs on the raw slabs exactly like the TF32 route.  Y is ~2^-11 of X, so eight
-// bits of it are enough: it runs as kind::f16 MMAs on bf16(lo) x bf16(hi) (4x the tf32 rate; rounding, not
-// truncation, so its error does not accumulate).  Four "loader" warps (2, 3, 8, 9 -- together they may touch
-// all four TMEM lane quarters) read each landed slab once, row per lane, and write bf16(lo) straight into
-// TENSOR MEMORY as the A operand of the Y MMAs (tcgen05.st, two K elements per 32-bit column; eight 16-column
-// buffers) and bf16(hi) into a half-size slab of the stage as their B operand.
+// X3 = true: fp32-grade result from two tf32 products per K step in ONE instruction.  With hi = trunc_tf32(x)
+// (what the tensor core sees of an fp32 operand -- measured: it truncates) and lo = x - hi,
+// S = X + Y + Y^T where X = hi.hi^T and Y = hi.lo^T (lo.lo^T < 2^-20 is dropped).  The third product of the
+// classic 3xTF32 scheme is the transpose of the second, so it is never computed: the epilogue folds Y in
+// twice, once along its row and once, through a warp transpose-sum, along its column.  Four "transform" warps
+// (2, 3, 8, 9) write lo of every landed slab into a twin slab right behind it (same swizzled layout, so the
+// transform is purely elementwise), and the issuer runs one M = 128, N = 256 MMA per K step whose B operand is
+// the 256-row pair [raw slab ; lo slab]: the accumulator tile is [X | Y] (2 x 256 TMEM columns, double buffered).
+// The raw slabs of a stage arrive as one-slab TMA boxes so that each can sit in front of its twin.
 // The tensor core's fp32 accumulator truncates when it aligns addends: over the MMAs of a D = 3072 request
 // the diagonal drifted by ~1e-5 relative (measured), too much for the 1e-5 bar.  So X accumulates in CHUNKS
-// of kTcChunkSlabs slabs: two TMEM accumulators alternate per chunk, and the epilogue threads add each
-// finished chunk into fp32 registers (round-to-nearest adds), which bounds every in-TMEM accumulation chain
-// to 64 MMAs.  Y's drift does not matter and it accumulates over the whole request in one (single-buffered)
-// TMEM accumulator that the epilogue drains first.  Because the epilogue threads are on the accumulator
-// hand-off path every eight slabs, their own global loads (votes, weights) are issued in batches.
-// This route is bound by the tensor pipe and its hand-offs: a kind::tf32 M=128 N=128 K=8 MMA occupies the pipe
-// for 128 clk (ncu: tf32 peak 1,024 FMA/clk/SM) and a kind::f16 one of K=16 as long (shared-memory operand
-// fetch, 64 B/clk), so a 16 KB slab costs >= 4 x 128 + 2 x 64..128 clk against the ~600 clk it has at HBM speed.
-// History (cfg4, 8,192 requests; the TF32 route takes 1.9 ms on the same boxes): three N=128 tf32 MMAs per K
-// step, all operands in shared memory 4.02 ms -> two MMAs with the symmetric fold 3.6 ms -> one N=256 MMA on
-// [raw ; lo] 3.36-3.52 ms at 94 % tensor-pipe occupancy -> bf16 correction product with a TMEM A operand
-// 3.5 ms until the epilogue's vote / weight loads were batched (a load-test-load chain per voter had kept the
-// epilogue threads away from the accumulator hand-offs for two chunks per request), then 3.0-3.1 ms.
-// profiles/r1_kernel_history.md has the full table.
-// Bound: TF32 route HBM (tensor pipe ~85 % busy at HBM speed); X3 route tensor pipe + hand-offs.
+// of kTcChunkSlabs slabs: the two accumulators alternate per chunk and the epilogue threads add each finished X
+// into fp32 registers (round-to-nearest adds), which bounds every in-TMEM chain to 32 MMAs.  Y is ~2^-11 of X,
+// so its drift does not matter and it must NOT restart per chunk (there are no registers left to sum it in):
+// the MMAs therefore always accumulate, and the epilogue zeroes what has to restart with tcgen05.st -- the X
+// half after each chunk, the two Y halves (even chunks' Y in one accumulator, odd chunks' in the other) after
+// reading them at the end of the request.
+// Because the epilogue threads are on the accumulator hand-off path every eight slabs, their own global loads
+// (votes, weights) are issued in batches: as a load-test-load chain per voter they stalled the MMA issuer.
+// This route is TENSOR-bound: an M=128 N=256 K=8 kind::tf32 MMA takes ~141 ns whatever the SM clock (276 clk
+// at 1.965 GHz; 550 TFLOP/s per GPU; ncu's tf32 peak is 1,024 FMA/clk/SM, a quarter of bf16), so the four MMAs
+// of a 16 KB slab take ~564 ns against the ~345 ns a slab has at HBM speed.
+// History (cfg4, 8,192 requests): three N = 128 MMAs, all operands in shared memory 4.02 ms -> two MMAs with
+// the symmetric fold 3.6 ms -> A operands from tensor memory (tcgen05.st by row-loader warps, tcgen05.mma with
+// a TMEM A) 3.6 ms, which showed that shared-memory bandwidth was not the limit -> one N = 256 MMA 3.36-3.52 ms
+// -> batched epilogue loads 2.93-3.11 ms = the tensor roofline of the scheme.  Moving the correction product to
+// kind::f16 (bf16 lo as a TMEM A operand x bf16 hi) was as fast but used up to 1.3x the stated tolerance.
+// Bound: TF32 route HBM (tensor pipe ~85 % busy at HBM speed); X3 route tensor.
 #pragma once
 
 #include <cuda.h>
-#include <cuda_bf16.h>
 
 #include "score_stream.cuh"
 
 namespace lwc {
 
 constexpr int kTcThreads = 256;   // TF32 route: producer, issuer, TMEM allocator, spare, 4 epilogue warps
-constexpr int kTcThreadsX3 = 320; // + warps 8, 9; warps 2, 3, 8, 9 are the loaders
+constexpr int kTcThreadsX3 = 320; // + warps 8, 9; warps 2, 3, 8, 9 transform
 constexpr int kTcSlabBytes = 128 * 128;  // one [128 rows x 32 fp32] operand slab, SWIZZLE_128B
 constexpr int kTcMaxStages = 8;
-constexpr int kTcABufs = 8;      // X3: A-operand buffers in tensor memory (16 columns = bf16 lo of one raw slab each)
-// X3 tensor-memory map (512 columns): X chunk accumulators 0 / 128, Y 256, A buffers 384 + 16 * buf
-constexpr uint32_t kTcColY = 256, kTcColA = 384;
-constexpr int kTcChunkSlabs = 16; // X3: operand slabs (64 MMAs into X) per in-TMEM accumulation chunk
+constexpr int kTcChunkSlabs = 8;  // X3: operand slabs (32 MMAs into X) per in-TMEM accumulation chunk
 #ifndef LWC_TC_ROUND
 #define LWC_TC_ROUND 0u
 #endif
@@ -108,39 +105,16 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
-// Instruction descriptor: D = F32, A = B = BF16 (1), both K-major.
-__device__ __forceinline__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
-
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                          uint32_t accumulate) {
+// 32 consecutive columns of this thread's TMEM lane <- registers.
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
     asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-
-// The same with the A operand in TENSOR MEMORY: lane = row, each 32-bit column holds two consecutive K
-// elements (8 columns = one K = 16 step).
-__device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
-                                             uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// 16 consecutive columns of this thread's TMEM lane <- registers.
-__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
-        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
         ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
-          "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+          "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+          "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+          "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
         : "memory");
 }
 // All MMAs issued so far by this thread arrive on `bar` when they complete (implies fence::before_thread_sync).
@@ -175,11 +149,11 @@ __global__ void __launch_bounds__(X3 ? kTcThreadsX3 : kTcThreads, 1)
 score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, const TcGeom geo) {
     extern __shared__ __align__(1024) unsigned char smem_tc[];
     const int KO = geo.ko, S = geo.stages;
-    // A stage is one TMA box of KO raw slabs; X3 appends KO/2 slabs of bf16(hi), the B operand of the correction
-    // product for the same K range (a bf16 slab row holds 64 columns = two raw slabs).
-    const int rawb = KO * kTcSlabBytes;
-    const int stageb = X3 ? rawb + (rawb >> 1) : rawb;
-    constexpr int NTW = 4;                         // loader warps (X3 only)
+    // TF32 route: a stage is one TMA box of KO slabs.  X3: a stage is KO pairs [raw slab][lo slab], each pair
+    // the 256-row B operand of one N = 256 MMA; the raw slabs arrive as KO one-slab boxes.
+    constexpr int kSlabStride = (X3 ? 2 : 1) * kTcSlabBytes;
+    const int stageb = KO * kSlabStride;
+    constexpr int NTW = 4;                         // transform warps (X3 only)
     // dynamic shared memory is only guaranteed 16-byte aligned: SWIZZLE_128B tiles need 1024
     unsigned char *ring = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_tc) + 1023) & ~(uintptr_t)1023);
     float *u_s = reinterpret_cast<float *>(ring + (size_t)S * stageb); // [128] t_i / n_i
@@ -190,10 +164,9 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
     uint64_t *bars = reinterpret_cast<uint64_t *>(tmem_slot + 2);     // full[S], empty[S], tfull[2], tempty[2], ready[S], yempty[2]
     const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * kTcMaxStages;
     const uint32_t tfull0 = empty0 + 8 * kTcMaxStages, tempty0 = tfull0 + 16;
-    const uint32_t ready0 = tempty0 + 16; // X3, per A buffer: bf16(lo) of a raw slab is in tensor memory, bf16(hi) in the stage
-    const uint32_t yempty0 = ready0 + 8 * kTcMaxStages; // X3: the request's Y accumulator has been read ([0] only)
-    const uint32_t afree0 = yempty0 + 16;               // X3, per A buffer: the MMAs that read it have completed
-    float *col_s = reinterpret_cast<float *>(bars + 4 * kTcMaxStages + 6); // X3: [4][128] column sums of u_i Y_ij per warp
+    const uint32_t ready0 = tempty0 + 16; // X3: the stage's lo slabs are written and visible to the tensor core
+    const uint32_t yempty0 = ready0 + 8 * kTcMaxStages; // X3: both Y accumulators have been read and zeroed
+    float *col_s = reinterpret_cast<float *>(bars + 3 * kTcMaxStages + 6); // X3: [4][128] column sums of u_i Y_ij per warp
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int N = p.N, D = p.D, M = p.M;
@@ -208,10 +181,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         for (int s = 0; s < S; ++s) {
             mbar_init(full0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, 1);
-        }
-        for (int s = 0; s < kTcABufs; ++s) {
             mbar_init(ready0 + 8 * s, NTW);
-            mbar_init(afree0 + 8 * s, 1);
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(tfull0 + 8 * b, 1);
@@ -220,7 +190,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    constexpr uint32_t kTmemCols = X3 ? 512 : 256; // two 128 x 128 fp32 accumulators; X3: + Y + the A buffers
+    constexpr uint32_t kTmemCols = X3 ? 512 : 256; // two accumulators: 128 x 128 fp32, or X3: 128 x 256 = [X | Y]
     if (warp == 2) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols)
                      : "memory");
@@ -230,6 +200,21 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (X3) {
+        // X3 MMAs always accumulate (the N = 256 tile holds X, restarted per chunk, beside Y, which is not),
+        // so the epilogue threads zero what must restart; at the start, everything.
+        if (warp >= 4 && warp < 8) {
+            uint32_t z[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) z[e] = 0u;
+            for (int c = 0; c < 16; ++c) tmem_st32(tmem_base + ((uint32_t)((warp - 4) * 32) << 16) + (uint32_t)(c * 32), z);
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        }
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+    }
+
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
@@ -239,8 +224,16 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
             for (int q = 0; q < nreq; ++q)
                 for (int s = 0; s < spr; ++s) {
                     mbar_wait_backoff(empty0 + 8 * slot, phase ^ 1u, 40);
-                    mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)rawb); // OOB zero-fill counts too
-                    tma_load_4d(ring_u32 + slot * stageb, &tmE, 0, 0, s * KO, r_begin + q, full0 + 8 * slot);
+                    if (X3) { // one box per slab, into the first half of its [raw][lo] pair
+                        const int nk = min(KO, nslab - s * KO);
+                        mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)(nk * kTcSlabBytes));
+                        for (int k = 0; k < nk; ++k)
+                            tma_load_4d(ring_u32 + slot * stageb + k * kSlabStride, &tmE, 0, 0, s * KO + k, r_begin + q,
+                                        full0 + 8 * slot);
+                    } else {
+                        mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)(KO * kTcSlabBytes)); // OOB zero-fill counts too
+                        tma_load_4d(ring_u32 + slot * stageb, &tmE, 0, 0, s * KO, r_begin + q, full0 + 8 * slot);
+                    }
                     if (++slot == S) {
                         slot = 0;
                         phase ^= 1u;
@@ -252,19 +245,18 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         // ===================== MMA issuer =====================
         if (lane == 0) {
             const uint32_t ring_u32 = smem_u32(ring);
-            const uint32_t idesc = umma_idesc_tf32(128, 128), idesc_y = umma_idesc_bf16(128, 128);
+            const uint32_t idesc = umma_idesc_tf32(128, X3 ? 256 : 128);
+            constexpr uint32_t kAccCols = X3 ? 256u : 128u;
             int slot = 0;
             uint32_t phase = 0;
             uint32_t tile = 0; // accumulator hand-offs so far: one per request (TF32) or per chunk (X3)
-            uint32_t gs = 0;   // X3: raw slabs so far; A buffer gs % kTcABufs
             for (int q = 0; q < nreq; ++q) {
                 uint32_t ab = tile & 1u;
                 mbar_wait(tempty0 + 8 * ab, ((tile >> 1) & 1u) ^ 1u); // accumulator drained by the epilogue
                 tc_fence_after();
-                uint32_t d_tmem = tmem_base + ab * 128u;
-                uint32_t acc = 0, accy = 0;
-                const uint32_t y_tmem = tmem_base + kTcColY;
-                if (X3) { // the single request-long Y accumulator: drained by the epilogue of the previous request
+                uint32_t d_tmem = tmem_base + ab * kAccCols;
+                uint32_t acc = 0;
+                if (X3) { // both Y halves drained and zeroed by the epilogue of the previous request
                     mbar_wait(yempty0, ((uint32_t)q & 1u) ^ 1u);
                     tc_fence_after();
                 }
@@ -275,37 +267,20 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                         ab = tile & 1u;
                         mbar_wait(tempty0 + 8 * ab, ((tile >> 1) & 1u) ^ 1u);
                         tc_fence_after();
-                        d_tmem = tmem_base + ab * 128u;
-                        acc = 0;
+                        d_tmem = tmem_base + ab * kAccCols;
                     }
-                    mbar_wait_backoff(full0 + 8 * slot, phase, 20);
+                    mbar_wait_backoff((X3 ? ready0 : full0) + 8 * slot, phase, 20); // X3: ready implies full
                     tc_fence_after();
                     const int nk = min(KO, nslab - s * KO);
-                    const uint32_t stage = ring_u32 + slot * stageb;
                     for (int k = 0; k < nk; ++k) {
-                        const uint32_t slab = stage + k * kTcSlabBytes;
+                        const uint32_t slab = ring_u32 + slot * stageb + k * kSlabStride;
 #pragma unroll
-                        for (int kk = 0; kk < 4; ++kk) { // 4 x K=8 inside the 128-byte swizzle atom: X += hi hi^T
-                            const uint64_t d = umma_desc_sw128(slab + kk * 32); // the SAME tile as A and as B
-                            umma_tf32(d_tmem, d, d, idesc, acc);
+                        for (int kk = 0; kk < 4; ++kk) { // 4 x K=8 inside the 128-byte swizzle atom
+                            // A: the raw slab (hi to the tensor core).  B: the same start address -- 128 rows
+                            // (TF32 route: S += hi hi^T) or 256 rows = [raw ; lo] (X3: [X | Y] += hi [hi ; lo]^T)
+                            const uint64_t d = umma_desc_sw128(slab + kk * 32);
+                            umma_tf32(d_tmem, d, d, idesc, X3 ? 1u : acc);
                             acc = 1;
-                        }
-                    }
-                    if (X3) {
-                        // Y += bf16(lo) bf16(hi)^T, two K = 16 steps per raw slab: A from the slab's buffer in tensor
-                        // memory, B from the stage's bf16(hi) slab (both written by the loader warps)
-                        for (int k = 0; k < nk; ++k, ++gs) {
-                            const uint32_t buf = gs % kTcABufs;
-                            mbar_wait(ready0 + 8 * buf, (gs / kTcABufs) & 1u);
-                            tc_fence_after();
-                            const uint32_t a_lo = tmem_base + kTcColA + buf * 16u;
-                            const uint32_t hib = stage + rawb + (uint32_t)(k >> 1) * kTcSlabBytes + (uint32_t)(k & 1) * 64u;
-#pragma unroll
-                            for (int k2 = 0; k2 < 2; ++k2) {
-                                umma_bf16_ts(y_tmem, a_lo + k2 * 8, umma_desc_sw128(hib + k2 * 32), idesc_y, accy);
-                                accy = 1;
-                            }
-                            umma_commit(afree0 + 8 * buf);
                         }
                     }
                     umma_commit(empty0 + 8 * slot); // stage reusable once these MMAs have read it
@@ -320,102 +295,42 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         }
         __syncwarp();
     } else if (X3 && (warp == 2 || warp == 3 || warp >= 8)) {
-        // ===================== loaders: raw slabs -> bf16(lo) in tensor memory, bf16(hi) in the stage =====================
-        // A warp may touch TMEM lanes 32 * (warp % 4) ..+31: warps 2, 3, 8, 9 cover the quarters 2, 3, 0, 1.
-        // Lane = row: it reads its row's 32 floats of each swizzled slab (8 x 16 B; the swizzle spreads the eight
-        // rows of a quarter-warp over all banks), stores bf16(x - trunc_tf32(x)) as 16 TMEM columns (two K
-        // elements per column) and bf16(x) as 4 x 16 B of its row of the stage's bf16 slab (same swizzle).
-        // Two slabs are in flight per lane (all loads first, then the conversions), and the TMEM stores of a
-        // pair complete (wait::st) while the next pair is read and converted.
-        const uint32_t r = (uint32_t)((warp & 3) * 32 + lane), sw = r & 7u;
-        const uint32_t lane_taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + kTcColA;
+        // ===================== transform: lo = x - trunc_tf32(x), slab by slab =====================
+        // Same swizzled layout in the twin slab, so the transform is purely elementwise (16 B per lane,
+        // lanes contiguous: conflict-free).
+        const int tw = warp < 4 ? warp - 2 : warp - 6; // 0..3
         int slot = 0;
-        uint32_t phase = 0, gs = 0;
-        int pend0 = -1, pend1 = -1; // A buffers whose tcgen05.st has been issued but not yet waited for / announced
+        uint32_t phase = 0;
         for (int q = 0; q < nreq; ++q)
             for (int s = 0; s < spr; ++s) {
                 mbar_wait_backoff(full0 + 8 * slot, phase, 40);
                 const int nk = min(KO, nslab - s * KO);
-                const uint32_t stage = smem_u32(ring) + (uint32_t)slot * (uint32_t)stageb;
-                for (int k = 0; k < nk; k += 2) {
-                    const bool two = k + 1 < nk;
-                    const uint32_t src = stage + (uint32_t)k * kTcSlabBytes + r * 128u;
-                    const uint32_t dst = stage + (uint32_t)rawb + (uint32_t)(k >> 1) * kTcSlabBytes + r * 128u;
-                    float4 x[2][8];
-#pragma unroll
-                    for (int j = 0; j < 2; ++j)
-#pragma unroll
-                        for (int c = 0; c < 8; ++c) {
-                            if (j == 1 && !two) {
-                                x[j][c] = make_float4(0.f, 0.f, 0.f, 0.f);
-                                continue;
-                            }
-                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
-                                         : "=f"(x[j][c].x), "=f"(x[j][c].y), "=f"(x[j][c].z), "=f"(x[j][c].w)
-                                         : "r"(src + (uint32_t)j * kTcSlabBytes + (((uint32_t)c ^ sw) << 4)));
-                        }
-                    uint32_t lo[2][16];
-#pragma unroll
-                    for (int j = 0; j < 2; ++j)
-#pragma unroll
-                        for (int c = 0; c < 4; ++c) { // two raw 16-byte chunks -> one bf16 16-byte chunk
-                            const float xs[8] = {x[j][2 * c].x,     x[j][2 * c].y,     x[j][2 * c].z,     x[j][2 * c].w,
-                                                 x[j][2 * c + 1].x, x[j][2 * c + 1].y, x[j][2 * c + 1].z, x[j][2 * c + 1].w};
-                            uint32_t h[4];
-#pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                const float a = xs[2 * e], b = xs[2 * e + 1];
-                                const float la = a - __uint_as_float(__float_as_uint(a) & 0xffffe000u);
-                                const float lb = b - __uint_as_float(__float_as_uint(b) & 0xffffe000u);
-                                const __nv_bfloat162 hh = __floats2bfloat162_rn(a, b), ll = __floats2bfloat162_rn(la, lb);
-                                h[e] = *reinterpret_cast<const uint32_t *>(&hh);
-                                lo[j][c * 4 + e] = *reinterpret_cast<const uint32_t *>(&ll);
-                            }
-                            if (j == 0 || two)
-                                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (((uint32_t)(4 * j + c) ^ sw) << 4)),
-                                             "r"(h[0]), "r"(h[1]), "r"(h[2]), "r"(h[3])
-                                             : "memory");
-                        }
-                    if (pend0 >= 0) { // the previous pair: its TMEM stores and bf16(hi) chunks are done by now
-                        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-                        tc_fence_before();
-                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // the bf16(hi) chunks, for the tensor core
-                        __syncwarp();
-                        if (lane == 0) {
-                            mbar_arrive(ready0 + 8 * pend0);
-                            if (pend1 >= 0) mbar_arrive(ready0 + 8 * pend1);
-                        }
-                    }
-                    const uint32_t b0 = gs % kTcABufs;
-                    mbar_wait(afree0 + 8 * b0, ((gs / kTcABufs) & 1u) ^ 1u);
-                    tc_fence_after();
-                    tmem_st16(lane_taddr + b0 * 16u, lo[0]);
-                    pend0 = (int)b0, pend1 = -1;
-                    ++gs;
-                    if (two) {
-                        const uint32_t b1 = gs % kTcABufs;
-                        mbar_wait(afree0 + 8 * b1, ((gs / kTcABufs) & 1u) ^ 1u);
-                        tc_fence_after();
-                        tmem_st16(lane_taddr + b1 * 16u, lo[1]);
-                        pend1 = (int)b1;
-                        ++gs;
+                for (int k = 0; k < nk; ++k) {
+                    const uint32_t src = smem_u32(ring) + (uint32_t)slot * (uint32_t)stageb + (uint32_t)k * kSlabStride;
+#pragma unroll 4
+                    for (int idx = tw * 32 + lane; idx < kTcSlabBytes / 16; idx += NTW * 32) {
+                        float4 x, l;
+                        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                     : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w)
+                                     : "r"(src + (uint32_t)idx * 16u));
+                        l.x = x.x - __uint_as_float((__float_as_uint(x.x) + kTcRound) & 0xffffe000u);
+                        l.y = x.y - __uint_as_float((__float_as_uint(x.y) + kTcRound) & 0xffffe000u);
+                        l.z = x.z - __uint_as_float((__float_as_uint(x.z) + kTcRound) & 0xffffe000u);
+                        l.w = x.w - __uint_as_float((__float_as_uint(x.w) + kTcRound) & 0xffffe000u);
+                        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(src + (uint32_t)kTcSlabBytes + (uint32_t)idx * 16u),
+                                     "f"(l.x), "f"(l.y), "f"(l.z), "f"(l.w)
+                                     : "memory");
                     }
                 }
+                // generic-proxy writes must be visible to the tensor core (async proxy) before it is told
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(ready0 + 8 * slot);
                 if (++slot == S) {
                     slot = 0;
                     phase ^= 1u;
                 }
             }
-        if (pend0 >= 0) {
-            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-            tc_fence_before();
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(ready0 + 8 * pend0);
-                if (pend1 >= 0) mbar_arrive(ready0 + 8 * pend1);
-            }
-        }
     } else if (warp >= 4 && warp < 8) {
         // ===================== epilogue =====================
         const int i = threadIdx.x - 128;   // row of S owned by this thread == TMEM lane
@@ -456,29 +371,40 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                 float row[128];
 #pragma unroll
                 for (int e = 0; e < 128; ++e) row[e] = 0.f;
+                uint32_t z[32];
+#pragma unroll
+                for (int e = 0; e < 32; ++e) z[e] = 0u;
                 for (int ch = 0; ch < nchunk; ++ch, ++tile) {
                     const uint32_t ab = tile & 1u;
                     mbar_wait_backoff(tfull0 + 8 * ab, (tile >> 1) & 1u, 200);
                     tc_fence_after();
-                    const uint32_t row_addr = lane_addr + ab * 128u;
+                    const uint32_t row_addr = lane_addr + ab * 256u; // X half of the [X | Y] accumulator
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         tmem_ld32(row_addr + (uint32_t)(c * 32), v);
+                        tmem_st32(row_addr + (uint32_t)(c * 32), z); // X restarts with the accumulator's next chunk
 #pragma unroll
                         for (int e = 0; e < 32; ++e) row[c * 32 + e] += v[e];
                     }
-                    tc_fence_before();
-                    mbar_arrive(tempty0 + 8 * ab);
+                    if (ch + 1 < nchunk) {
+                        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                        tc_fence_before();
+                        mbar_arrive(tempty0 + 8 * ab);
+                    }
                 }
-                // The last chunk's commit covered every MMA of the request, so Y = lo.hi^T is complete too.  Y is
-                // single-buffered and the next request's MMAs wait for it, so it is drained before any block-wide
-                // step: its diagonal gives n_i, hence u_i = t_i / n_i, which is all a thread needs to scale ITS row
-                // of Y for the column sums; X + Y stays in row[].
-                const uint32_t y_addr = lane_addr + kTcColY;
-                tmem_ld32(y_addr + (uint32_t)(ew * 32), v);
+                // The last chunk's commit covered every MMA of the request, so Y = hi.lo^T is complete too: it sits
+                // in the Y halves of BOTH accumulators (even chunks in one, odd chunks in the other).  The next
+                // request's MMAs wait for Y, so it is drained (and zeroed) before any block-wide step: the diagonal
+                // gives n_i, hence u_i = t_i / n_i, which is all a thread needs to scale ITS row of Y for the
+                // column sums; X + Y stays in row[].
+                const uint32_t last_ab = (tile - 1u) & 1u;
                 float yd = 0.f;
 #pragma unroll
-                for (int e = 0; e < 32; ++e) yd = (lane == e) ? v[e] : yd;
+                for (int h = 0; h < 2; ++h) {
+                    tmem_ld32(lane_addr + (uint32_t)h * 256u + 128u + (uint32_t)(ew * 32), v);
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) yd += (lane == e) ? v[e] : 0.f;
+                }
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
 #pragma unroll
@@ -490,15 +416,24 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                 // sum_j u_j S_ij = sum_j u_j (X_ij + Y_ij)  [own row]  +  sum_j u_j Y_ji  [column i of u_j-scaled Y]
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
-                    tmem_ld32(y_addr + (uint32_t)(c * 32), v);
+                    float cs = 0.f;
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) {
-                        row[c * 32 + e] += v[e];
-                        v[e] *= ui;
+                    for (int h = 0; h < 2; ++h) {
+                        const uint32_t ya = lane_addr + (uint32_t)h * 256u + 128u + (uint32_t)(c * 32);
+                        tmem_ld32(ya, v);
+                        tmem_st32(ya, z);
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) {
+                            row[c * 32 + e] += v[e];
+                            v[e] *= ui;
+                        }
+                        cs += warp_transpose_sum<32>(v, lane); // rows of this warp, column 32c + lane
                     }
-                    col_s[ew * 128 + c * 32 + lane] = warp_transpose_sum<32>(v, lane); // rows of this warp, column 32c + lane
+                    col_s[ew * 128 + c * 32 + lane] = cs;
                 }
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
                 tc_fence_before();
+                mbar_arrive(tempty0 + 8 * last_ab); // the last chunk's X half, zeroed in the loop above
                 mbar_arrive(yempty0);
                 epi_sync();
 #pragma unroll
@@ -609,7 +544,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
 }
 
 inline size_t tc_smem_bytes(int ko, int stages, bool x3) {
-    return 1024 + (size_t)stages * ko * kTcSlabBytes * (x3 ? 3 : 2) / 2 + (128 + 128 + 16 + 8 + 2) * 4 + (4 * kTcMaxStages + 6) * 8 +
+    return 1024 + (size_t)stages * ko * kTcSlabBytes * (x3 ? 2 : 1) + (128 + 128 + 16 + 8 + 2) * 4 + (3 * kTcMaxStages + 6) * 8 +
            (x3 ? 4 * 128 * 4 : 0) + 64;
 }
 

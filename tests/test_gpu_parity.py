@@ -371,6 +371,27 @@ def test_large_pool_tcgen05_route(ctx, lwc, oracle, shape, memory):
     properties_hold(got, V)
 
 
+@pytest.mark.parametrize("shape", TC_SHAPES + [(3, 128, 32, 2), (4, 77, 160, 5)], ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+def test_large_pool_tcgen05_fp32_grade_route(ctx, lwc, oracle, shape):
+    """The same shapes at the default precision: tf32 product + bf16 correction product, within the fp32 bar.
+    D = 32, 96 and 160 leave the last stage / the last bf16 slab half filled."""
+    from lwc_b200 import synth
+
+    R, N, D, M = shape
+    assert ctx.kernel_for(R, N, D, M) == "tc128_tf32x3"
+    E, V, w, _ = synth.make_batch(R, N, D, M, seed=777 + N + D, edge_cases=False)
+    if R > 3:
+        V[1] = np.nan
+        E[2, N - 1] = 0.0      # zero-norm candidate
+        w[3, 0] = np.nan
+    got = ctx.score_batch(E, V, w)
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    assert compare(got, want, V) == 1.0
+    properties_hold(got, V)
+    again = ctx.score_batch(E, V, w)
+    assert all(np.array_equal(got[k], again[k], equal_nan=True) for k in got)  # run-to-run reproducible
+
+
 def test_large_pool_exact_tie_and_order_invariance(ctx, lwc):
     rng = np.random.default_rng(8)
     R, N, D, M = 40, 128, 512, 2
