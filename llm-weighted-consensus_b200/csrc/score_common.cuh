@@ -108,12 +108,24 @@ __device__ __forceinline__ void warp_tally_and_rank_pf(const ScoreParams &p, int
             if (!isnan(v0) && act) t = fmaf(pv[m], wm, t);
         }
     }
-    for (int m = MU; m < M; ++m) {
-        const float v0 = __ldg(Vr + (size_t)m * N);
-        if (isnan(v0)) continue; // voter without a vote (client.rs:410) -- warp-uniform
-        float wm = __ldg(wr + m);
-        if (isnan(wm)) wm = 0.f; // weight None -> 0 (client.rs:412-413)
-        if (act) t = fmaf(__ldg(Vr + (size_t)m * N + lane), wm, t);
+    // the voters that were not prefetched: eight voters' loads in flight at a time (a load-test-load chain per
+    // voter costs ~1.5 k clk each, during which this warp's CTA streams nothing)
+    for (int m0 = MU; m0 < M; m0 += 8) {
+        float v0[8], wv[8], vl[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int m = m0 + u;
+            const bool ok = m < M;
+            v0[u] = ok ? __ldg(Vr + (size_t)m * N) : __int_as_float(0x7fc00000);
+            wv[u] = ok ? __ldg(wr + m) : 0.f;
+            vl[u] = (ok && act) ? __ldg(Vr + (size_t)m * N + lane) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            if (isnan(v0[u])) continue; // voter without a vote (client.rs:410) -- warp-uniform
+            const float wm = isnan(wv[u]) ? 0.f : wv[u]; // weight None -> 0 (client.rs:412-413)
+            if (act) t = fmaf(vl[u], wm, t);
+        }
     }
 
     float c = t;
@@ -170,15 +182,21 @@ __device__ __forceinline__ void warp_tally_and_rank_pf(const ScoreParams &p, int
                 if (lane == 0) p.agree[(size_t)r * M + m] = isnan(v0) ? __int_as_float(0x7fc00000) : part[m];
             }
         }
-        for (int m = MU; m < M; ++m) {
-            const float v0 = __ldg(Vr + (size_t)m * N);
-            float a;
-            if (isnan(v0)) {
-                a = __int_as_float(0x7fc00000);
-            } else {
-                a = warp_sum(act ? cf * __ldg(Vr + (size_t)m * N + lane) : 0.f);
+        for (int m0 = MU; m0 < M; m0 += 8) {
+            float v0[8], vl[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int m = m0 + u;
+                v0[u] = m < M ? __ldg(Vr + (size_t)m * N) : 0.f;
+                vl[u] = (m < M && act) ? __ldg(Vr + (size_t)m * N + lane) : 0.f;
             }
-            if (lane == 0) p.agree[(size_t)r * M + m] = a;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int m = m0 + u;
+                if (m >= M) break;
+                const float a = isnan(v0[u]) ? __int_as_float(0x7fc00000) : warp_sum(act ? cf * vl[u] : 0.f);
+                if (lane == 0) p.agree[(size_t)r * M + m] = a;
+            }
         }
     }
 }
