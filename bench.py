@@ -70,6 +70,7 @@ class ClockSampler(threading.Thread):
         self.samples = []
         self.reasons = set()
         self.stop_flag = False
+        self.active = False  # set by the main thread around the timed regions: nothing is queried outside them
         self.max_mhz = None
         self.ok = False
         try:
@@ -94,9 +95,12 @@ class ClockSampler(threading.Thread):
             getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
         }
         while not self.stop_flag:
+            if not self.active:
+                time.sleep(0.0005)
+                continue
             try:
                 mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
-                util = nv.nvmlDeviceGetUtilizationRates(self.h).gpu
+                util = 1
                 try:
                     mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
                 except Exception:
@@ -107,7 +111,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.002)
+            time.sleep(0.003)  # a few samples per timed region; every query contends with the launch path
 
     def summary(self):
         if not self.samples:
@@ -124,6 +128,23 @@ def host_cores():
         return max(1, len(os.sched_getaffinity(0)))
     except AttributeError:
         return max(1, os.cpu_count() or 1)
+
+
+def bind_to_gpu_numa_node(index):
+    """Pin this process to the CPUs next to its GPU (NVML's ideal affinity) before any pinned buffer is allocated
+    and touched, so the host side of every H2D copy is node-local memory: with 8 ranks pushing 55 GB/s each the
+    end-to-end rate is bound by host memory, and remote-node pages halve it.  Returns the previous CPU set."""
+    try:
+        import pynvml
+
+        before = os.sched_getaffinity(0)
+        pynvml.nvmlInit()
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(index))
+        if not os.sched_getaffinity(0):
+            os.sched_setaffinity(0, before)
+        return before
+    except Exception:
+        return None
 
 
 def cpu_baseline(E, V, w, budget_s=10.0):
@@ -192,6 +213,7 @@ def run_b200(args):
     if world != args.gpus and world > 1:
         raise SystemExit(f"WORLD_SIZE={world} but --gpus {args.gpus}")
     torch.cuda.set_device(local_rank)
+    all_cpus = bind_to_gpu_numa_node(local_rank)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -273,14 +295,22 @@ def run_b200(args):
     barrier()
     launches0 = ctx.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.active = True
     with torch.cuda.stream(stream):
         ev0.record(stream)
         for i in range(args.steps):
             step_device(i)
         ev1.record(stream)
     barrier()
+    sampler.active = False
     launches = ctx.launch_count() - launches0
-    dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    my_ms = ev0.elapsed_time(ev1)
+    dev_ms = max_over_ranks(my_ms)
+    per_rank_ms = [my_ms / args.steps]
+    if dist is not None:
+        tt = [torch.zeros(1, dtype=torch.float64, device="cuda") for _ in range(world)]
+        dist.all_gather(tt, torch.tensor([my_ms / args.steps], dtype=torch.float64, device="cuda"))
+        per_rank_ms = [float(x.item()) for x in tt]
     ms_per_step = dev_ms / args.steps
     value = world * R * args.steps / (dev_ms * 1e-3)
 
@@ -291,12 +321,14 @@ def run_b200(args):
     barrier()
     ext = torch.cuda.ExternalStream(ctx.stream())
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.active = True
     e0.record(ext)
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         step_host()
     e1.record(ext)
     barrier()
+    sampler.active = False
     wall_ms = (time.perf_counter() - t0) * 1e3
     e2e_ms = max_over_ranks(max(e0.elapsed_time(e1), 0.0))
     if e2e_ms <= 0:
@@ -326,7 +358,7 @@ def run_b200(args):
                    "l2": f"{n_rot} rotating input batches of {hE.nbytes / 1e6:.0f} MB each (> 126 MB L2)",
                    "launches": "serialised" if args.no_overlap else
                                "programmatic dependent launch: a launch streams its (resident) inputs while the previous one drains"},
-        "clocks": sampler.summary(),
+        "clocks": sampler.summary(), "per_rank_ms_per_step": per_rank_ms,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "wall_ms_per_step": wall_ms / e2e_steps,
                 "api": "lwc_score_batch(LWC_MEM_HOST), pinned host buffers"},
@@ -337,6 +369,8 @@ def run_b200(args):
         "host_device_paths_agree": same,
     }
     if world == 1 and not args.no_cpu_baseline:
+        if all_cpus:
+            os.sched_setaffinity(0, all_cpus)  # the CPU arm owns the whole box again
         line["cpu_baseline"] = cpu_baseline(hE.array, V, w)
     if rank == 0:
         print(json.dumps(line), flush=True)
