@@ -203,6 +203,49 @@ static int gpu_checks() {
                 REQUIRE(b.rank[0] == b.winner);
             }
         }
+    // from streamed chunks to the written-back aggregate (client.rs:362, 384-456) with the tally on the GPU:
+    // similarity = identity, so the expected numbers are the reference's own (golden K-style case)
+    {
+        namespace st = score::completions::response::streaming;
+        st::ChatCompletionChunk agg;
+        for (uint64_t i = 0; i < 3; ++i) {
+            st::Choice c;
+            c.index = i;
+            agg.choices.push_back(c);
+        }
+        const double votes[3][3] = {{0.5, 0.25, 0.25}, {0.0, 1.0, 0.0}, {0.125, 0.125, 0.75}};
+        const double weights[3] = {1.0, 2.0, 4.0};
+        for (int m = 0; m < 3; ++m) {
+            st::ChatCompletionChunk piece, last;
+            st::Choice c;
+            c.index = 3 + m;
+            c.delta.content = "thinking";
+            piece.choices.push_back(c);
+            c = st::Choice{};
+            c.index = 3 + m;
+            c.delta.vote = std::vector<double>(votes[m], votes[m] + 3);
+            c.weight = weights[m];
+            last.choices.push_back(c);
+            agg.push(piece);
+            agg.push(last);
+        }
+        const Request rq = score::completions::request_from_aggregate(agg, 3);
+        const Tally tl = batcher.submit(rq).get();
+        score::completions::apply_tally(agg, tl, 3);
+        const double cw[3] = {0.5 * 1 + 0.125 * 4, 0.25 * 1 + 1.0 * 2 + 0.125 * 4, 0.25 * 1 + 0.75 * 4};
+        const double sum = cw[0] + cw[1] + cw[2];
+        for (int j = 0; j < 3; ++j) {
+            REQUIRE(std::fabs(*agg.choices[j].weight - cw[j]) < 1e-6);
+            REQUIRE(std::fabs(*agg.choices[j].confidence - cw[j] / sum) < 1e-6);
+        }
+        for (int m = 0; m < 3; ++m) {
+            double a = 0;
+            for (int j = 0; j < 3; ++j) a += cw[j] / sum * votes[m][j];
+            REQUIRE(std::fabs(*agg.choices[3 + m].confidence - a) < 1e-6);
+            REQUIRE(!agg.choices[3 + m].delta.vote.has_value());
+        }
+        REQUIRE(tl.winner == 2 && tl.rank[0] == 2);
+    }
     // argument errors surface as ResponseError 400, like Error::ExpectedTwoOrMoreChoices would
     try {
         Request bad;
