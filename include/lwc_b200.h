@@ -27,6 +27,13 @@
  *   lwc_vote_from_logprobs . the numeric tail of get_vote, client.rs:1765-1791: exp(logprob) of
  *                            the sibling-leaf alternatives, accumulated per choice, divided by
  *                            the probability sum.
+ *   lwc_table_load /
+ *   lwc_table_weights ...... what weight::Fetcher<CTX, TrainingTableData> would compute -- the slot
+ *                            the reference ships as unimplemented!(), src/score/completions/weight.rs:99-117
+ *                            (config src/score/model/mod.rs:278-306, limits src/score/llm/mod.rs:663-688);
+ *                            build-defined policy, no reference arithmetic to match.
+ *   lwc_pool_consensus_static, lwc_comm_*, lwc_pool_p2p_*, lwc_host_* / lwc_device_* / lwc_memcpy,
+ *   lwc_ctx_* .............. no reference counterpart (allocation-free variant, multi-GPU plumbing, lifecycle).
  *
  * Error convention mirrors error::ResponseError { code: u16, .. } (src/error.rs:8-13):
  * every function returns 0 on success or an HTTP-style status -- 400 for a malformed
