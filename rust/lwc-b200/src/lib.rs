@@ -8,6 +8,8 @@ use rust_decimal::Decimal;
 use std::ffi::CStr;
 use std::sync::Arc;
 
+pub mod batcher;
+
 /// One context per GPU.  `Send + Sync`: the library serialises calls on a context internally.
 pub struct Context(*mut sys::lwc_ctx);
 unsafe impl Send for Context {}
@@ -98,6 +100,21 @@ pub fn score_request(
         voter_confidence: (0..m).map(|i| if agree[i].is_nan() { None } else { Some(dec(agree[i])) }).collect(),
         winner: if winner[0] >= 0 { Some(winner[0] as usize) } else { None },
         rank: rank.iter().map(|&x| x as usize).collect(),
+    })
+}
+
+/// The same through the per-GPU batcher: the request joins whatever else is pending with its shape and the
+/// caller awaits the reply without ever blocking a tokio worker inside CUDA.
+pub async fn score_request_batched(
+    batcher: &batcher::Batcher,
+    n_choices: usize,
+    votes: &[Option<&[Decimal]>],
+    weights: &[Option<Decimal>],
+    embeddings: Option<&embeddings::response::CreateEmbeddingResponse>,
+) -> Result<Scored, ResponseError> {
+    let rx = batcher.submit(n_choices, votes, weights, embeddings)?;
+    rx.await.unwrap_or_else(|_| {
+        Err(ResponseError { code: 500, message: serde_json::Value::String("batcher dropped the request".into()) })
     })
 }
 
