@@ -439,8 +439,11 @@ def run_other_workload(args, torch, lwc_b200, synth, local_rank, rank=0, world=1
     nbytes = R * synth.algorithmic_bytes_per_request(N, D, M)  # per GPU: the roofline is a per-GPU statement
     flops = R * synth.algorithmic_flops_per_request(N, D, M)
     achieved = nbytes / (ms * 1e-3) / 1e9
+    extra = {}
+    if args.e2e and world == 1:
+        extra = side_e2e_and_cpu(args, torch, lwc_b200, synth, ctx, N, D, M, prec)
     if rank == 0:
-        print(json.dumps({
+        print(json.dumps({**extra,
             "metric": f"scored requests/sec ({N}×{D} emb)", "value": R_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "scaling": "strong", "dtype": "f32",
             "data": "synthetic (generated in HBM)",
@@ -456,6 +459,51 @@ def run_other_workload(args, torch, lwc_b200, synth, local_rank, rank=0, world=1
     if dist is not None:
         dist.destroy_process_group()
     return 0
+
+
+def side_e2e_and_cpu(args, torch, lwc_b200, synth, ctx, N, D, M, prec):
+    """--e2e on a side workload: the same shape through lwc_score_batch(LWC_MEM_HOST) with pinned host buffers
+    (copies inside the timed region), and the CPU port on a bounded sample, so that the end-to-end ratio can be
+    read at pool sizes where the Gram dominates the CPU cost."""
+    Rh = 2048 if N * D <= 32 * 3072 else 1024
+    E, V, w, _ = synth.make_batch(Rh, N, D, M, seed=5, edge_cases=False)
+    hE, hV, hw = (lwc_b200.HostBuffer(ctx, a.shape, np.float32) for a in (E, V, w))
+    hE.array[...], hV.array[...], hw.array[...] = E, V, w
+    outs = [lwc_b200.HostBuffer(ctx, (Rh, N), np.float32), lwc_b200.HostBuffer(ctx, (Rh, N), np.float32),
+            lwc_b200.HostBuffer(ctx, (Rh, M), np.float32), lwc_b200.HostBuffer(ctx, (Rh,), np.int32),
+            lwc_b200.HostBuffer(ctx, (Rh, N), np.int32)]
+    desc = lwc_b200.BatchDesc(Rh, N, D, M, lwc_b200.SIM_COSINE, prec, lwc_b200.MEM_HOST, 1)
+
+    def step():
+        ctx.score_raw(desc, hE.ptr, hV.ptr, hw.ptr, *[o.ptr for o in outs])
+
+    for _ in range(2):
+        step()
+    ext = torch.cuda.ExternalStream(ctx.stream())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(ext)
+    for _ in range(5):
+        step()
+    e1.record(ext)
+    torch.cuda.synchronize()
+    e2e_ms = e0.elapsed_time(e1) / 5
+    out = {"e2e": {"value": Rh / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms, "requests_per_step": Rh,
+                   "h2d_bytes_per_step": hE.nbytes + hV.nbytes + hw.nbytes, "d2h_bytes_per_step": sum(o.nbytes for o in outs),
+                   "api": "lwc_score_batch(LWC_MEM_HOST), pinned host buffers"}}
+    if not args.no_cpu_baseline:
+        import oracle
+
+        cores = host_cores()
+        n = min(Rh, 256)
+        t, reps = 0.0, 0
+        while t < 5.0 and reps < 64:
+            t += oracle.score_port(E[:n], V[:n], w[:n], oracle.SIM_COSINE, nthreads=cores)["seconds"]
+            reps += 1
+        out["cpu_baseline"] = {"value": n * reps / t, "unit": UNIT, "cores": cores, "kind": "port",
+                               "sample": f"{reps} pass(es) over {n} requests of this shape"}
+    for b in (hE, hV, hw, *outs):
+        b.free()
+    return out
 
 
 def run_pool_workload(args, torch, lwc_b200, local_rank):
@@ -560,6 +608,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e", action="store_true", help="side workloads cfg3/cfg4: add the host-buffer path and the CPU port")
     ap.add_argument("--no-overlap", action="store_true", help="do not set LWC_CTX_INPUTS_RESIDENT (launches fully serialised)")
     ap.add_argument("--workload", default=WORKLOAD, choices=["cfg2", "cfg3", "cfg4", "cfg2x4", "pool", "table"],
                     help="cfg2 is the bench line; cfg3/cfg4 are kernel-only side measurements")
