@@ -392,6 +392,8 @@ def run_other_workload(args, torch, lwc_b200, synth, local_rank, rank=0, world=1
         return run_pool_workload(args, torch, lwc_b200, local_rank)
     if args.workload == "table":
         return run_table_workload(args, torch, lwc_b200, local_rank)
+    if args.workload == "vote":
+        return run_vote_workload(args, torch, lwc_b200, local_rank)
     R_total, N, D, M = synth.CONFIGS[args.workload]
     if args.requests:
         R_total = args.requests
@@ -560,6 +562,50 @@ def run_pool_workload(args, torch, lwc_b200, local_rank):
     return 0
 
 
+def run_vote_workload(args, torch, lwc_b200, local_rank):
+    """Side measurement of vote production: rows of 20 top-logprob alternatives -> vote rows of 16
+    choices, written where the scorer reads them.  HBM-bound: 8 bytes in per alternative, 4 out per choice."""
+    import ctypes
+
+    rows, top, N = (args.requests or 4_194_304), 20, 16
+    ctx = lwc_b200.Context(device=local_rank)
+    g = torch.Generator(device="cuda").manual_seed(3)
+    lp = -8.0 * torch.rand((rows, top), dtype=torch.float32, device="cuda", generator=g)
+    leaf = torch.randint(-4, N, (rows, top), dtype=torch.int32, device="cuda", generator=g)
+    V = torch.empty((rows, N), dtype=torch.float32, device="cuda")
+    vp = ctypes.c_void_p
+    st = torch.cuda.ExternalStream(ctx.stream())
+
+    def step():
+        rc = ctx.lib.lwc_vote_from_logprobs(ctx.handle, rows, top, N, vp(lp.data_ptr()), vp(leaf.data_ptr()), vp(V.data_ptr()),
+                                            lwc_b200.MEM_DEVICE, None)
+        if rc:
+            raise lwc_b200.LwcError(rc, ctx.lib.lwc_last_error_message(ctx.handle).decode())
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st)
+    for _ in range(args.steps):
+        step()
+    e1.record(st)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    nbytes = rows * (top * 8 + N * 4)
+    peak, src = load_peaks()
+    ach = nbytes / (ms * 1e-3) / 1e9
+    print(json.dumps({
+        "metric": "vote_rows_per_sec", "value": rows * 1e3 / ms, "unit": "rows/s", "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "dtype": "f32", "data": "synthetic (generated in HBM)",
+        "config": {"workload": f"vote: {rows} voter rows x {top} alternatives -> {N} choices", "kernel": "vote_from_logprobs"},
+        "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "peak_source": src,
+                     "bytes_per_launch": nbytes},
+        "row_sum": float(V[0].sum().item())}), flush=True)
+    ctx.close()
+    return 0
+
+
 def run_table_workload(args, torch, lwc_b200, local_rank):
     """Side measurement of the training-table weight lookup: 8 prompt embeddings per call
     against a resident table; the score pass streams the whole table from HBM once per call."""
@@ -610,7 +656,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e", action="store_true", help="side workloads cfg3/cfg4: add the host-buffer path and the CPU port")
     ap.add_argument("--no-overlap", action="store_true", help="do not set LWC_CTX_INPUTS_RESIDENT (launches fully serialised)")
-    ap.add_argument("--workload", default=WORKLOAD, choices=["cfg2", "cfg3", "cfg4", "cfg2x4", "pool", "table"],
+    ap.add_argument("--workload", default=WORKLOAD, choices=["cfg2", "cfg3", "cfg4", "cfg2x4", "pool", "table", "vote"],
                     help="cfg2 is the bench line; cfg3/cfg4 are kernel-only side measurements")
     ap.add_argument("--requests", type=int, default=0, help="override R for --workload cfg3/cfg4")
     ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32"])

@@ -625,9 +625,15 @@ int32_t lwc_vote_from_logprobs(lwc_ctx *ctx, int32_t n_rows, int32_t n_top, int3
         dlf = static_cast<const int32_t *>(s.buf[1]);
         dV = static_cast<float *>(s.buf[3]);
     }
-    const int warps = 4;
-    lwc::vote_from_logprobs_kernel<<<(n_rows + warps - 1) / warps, warps * 32, 0, st>>>(dlp, dlf, dV, n_rows, n_top,
-                                                                                     n_choices);
+    const size_t tile = lwc::vote_tile_smem(n_top, n_choices);
+    if (tile <= 48 * 1024) {
+        lwc::vote_tile_kernel<<<(n_rows + lwc::kVoteRows - 1) / lwc::kVoteRows, lwc::kVoteRows, tile, st>>>(dlp, dlf, dV, n_rows,
+                                                                                                            n_top, n_choices);
+    } else {
+        const int warps = 4;
+        lwc::vote_from_logprobs_kernel<<<(n_rows + warps - 1) / warps, warps * 32, 0, st>>>(dlp, dlf, dV, n_rows, n_top,
+                                                                                         n_choices);
+    }
     CUDA_TRY(ctx, cudaGetLastError());
     ctx->launches++;
     if (memory == LWC_MEM_HOST) {

@@ -3,7 +3,13 @@
 // p = exp(logprob) to vote[leaf]; the row is then divided by the probability sum
 // (client.rs:1789-1791).  The string/regex part of get_vote (client.rs:1669-1762) stays on the host
 // and produces (logprob, leaf) pairs; leaf < 0 marks an alternative that is not a sibling leaf.
-// One warp per vote row, rows written straight into the [R][M][N] vote buffer the scorer reads.
+// Rows are written straight into the [R][M][N] vote buffer the scorer reads.
+//
+// vote_tile_kernel (the route for ordinary shapes): HBM-bound, 8 bytes in per alternative and 4 out per choice.
+// A CTA stages kVoteRows rows through shared memory with coalesced 128-bit-wide traffic on both sides; each
+// thread then owns one row: one expf per alternative, accumulated into its row of the output tile in
+// alternative order (deterministic), then the row is divided by its probability sum.
+// vote_from_logprobs_kernel (one warp per row) remains for shapes whose tile does not fit 48 KB.
 #pragma once
 
 #include "score_common.cuh"
@@ -40,6 +46,57 @@ __global__ void __launch_bounds__(128) vote_from_logprobs_kernel(const float *__
         }
         out[j] = v / s;
     }
+}
+
+constexpr int kVoteRows = 128; // rows per CTA of vote_tile_kernel (= threads)
+
+inline size_t vote_tile_smem(int n_top, int n_choices) {
+    return (size_t)kVoteRows * ((size_t)n_top * 8 + (size_t)(n_choices + 1) * 4);
+}
+
+__global__ void __launch_bounds__(kVoteRows) vote_tile_kernel(const float *__restrict__ logprob,
+                                                              const int32_t *__restrict__ leaf, float *__restrict__ V,
+                                                              int n_rows, int n_top, int n_choices) {
+    extern __shared__ __align__(16) unsigned char vsm[];
+    float *lp_s = reinterpret_cast<float *>(vsm);                                   // [rows][n_top]
+    int32_t *lf_s = reinterpret_cast<int32_t *>(lp_s + (size_t)kVoteRows * n_top);  // [rows][n_top]
+    float *out_s = reinterpret_cast<float *>(lf_s + (size_t)kVoteRows * n_top);     // [rows][n_choices + 1]
+    const int pitch = n_choices + 1; // odd or even, consecutive rows start in different banks
+    const long long row0 = (long long)blockIdx.x * kVoteRows;
+    const int rows = (int)(n_rows - row0 < kVoteRows ? n_rows - row0 : kVoteRows);
+    const int n_in = rows * n_top;
+    const float *lp = logprob + (size_t)row0 * n_top;
+    const int32_t *lf = leaf + (size_t)row0 * n_top;
+    for (int i = threadIdx.x; i < n_in; i += kVoteRows) {
+        lp_s[i] = lp[i];
+        lf_s[i] = lf[i];
+    }
+    for (int i = threadIdx.x; i < rows * pitch; i += kVoteRows) out_s[i] = 0.f;
+    __syncthreads();
+    if ((int)threadIdx.x < rows) {
+        const float *x = lp_s + (size_t)threadIdx.x * n_top;
+        const int32_t *l = lf_s + (size_t)threadIdx.x * n_top;
+        float *o = out_s + (size_t)threadIdx.x * pitch;
+        float s = 0.f;
+        for (int k = 0; k < n_top; ++k) {
+            const int j = l[k];
+            const float v = x[k];
+            if (j >= 0 && j < n_choices && !isnan(v)) {
+                const float pk = expf(v);
+                o[j] += pk; // client.rs:1765-1784, in alternative order
+                s += pk;
+            }
+        }
+        if (s > 0.f) {
+            const float inv = 1.0f / s;
+            for (int j = 0; j < n_choices; ++j) o[j] *= inv; // client.rs:1789-1791
+        } else { // unreachable!() in the reference (client.rs:1786-1788): mark the voter absent
+            for (int j = 0; j < n_choices; ++j) o[j] = __int_as_float(0x7fc00000);
+        }
+    }
+    __syncthreads();
+    float *out = V + (size_t)row0 * n_choices;
+    for (int i = threadIdx.x; i < rows * n_choices; i += kVoteRows) out[i] = out_s[(i / n_choices) * pitch + i % n_choices];
 }
 
 } // namespace lwc

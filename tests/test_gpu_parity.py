@@ -321,24 +321,32 @@ def test_stage_f64(ctx, lwc):
     assert np.array_equal(dst, src.astype(np.float32))
 
 
-def test_vote_from_logprobs(ctx, lwc, oracle):
+@pytest.mark.parametrize("top,n", [(20, 37), (20, 16), (5, 2), (20, 128), (70, 16)],
+                         ids=["tile_20x37", "tile_20x16", "tile_5x2", "warp_rows_20x128", "warp_rows_70x16"])
+def test_vote_from_logprobs(ctx, lwc, oracle, top, n):
     """the numeric tail of get_vote (client.rs:1765-1791) on device.  The reference's
-    Decimal::exp is a truncated series (~1e-7); fp32 expf is compared to f64 exp at 1e-5 relative."""
+    Decimal::exp is a truncated series (~1e-7); fp32 expf is compared to f64 exp at 1e-5 relative.
+    Ordinary shapes take the shared-memory tile kernel, large ones the warp-per-row kernel."""
     rng = np.random.default_rng(21)
-    rows, top, n = 300, 20, 37
+    rows = 300
     lp = rng.normal(-2.0, 2.0, (rows, top)).astype(np.float32)
     leaf = rng.integers(-1, n, (rows, top)).astype(np.int32)
-    lp[5, 3] = np.nan          # logprob None
+    lp[5, min(3, top - 1)] = np.nan          # logprob None
     leaf[7] = -1               # no admissible alternative -> the reference's unreachable!(): absent voter
     V = ctx.vote_from_logprobs(lp, leaf, n)
     for r in range(rows):
         if r == 7:
             assert np.all(np.isnan(V[r]))
             continue
+        if not np.any((leaf[r] >= 0) & ~np.isnan(lp[r])):
+            assert np.all(np.isnan(V[r]))  # no admissible alternative in this random row either
+            continue
         want = oracle.vote_from_logprobs(n, lp[r].astype(np.float64), leaf[r])
         np.testing.assert_allclose(V[r], want, rtol=1e-5, atol=1e-8)
         assert abs(V[r].sum() - 1.0) < 1e-5
     # the rows feed the scorer directly: one-hot-like votes must keep the winner
+    if n < 3:
+        return
     E = rng.standard_normal((1, n, 64)).astype(np.float32)
     got = ctx.score_batch(E, V[None, :4], np.ones((1, 4), np.float32))
     want = oracle.score_f64(E, V[None, :4], np.ones((1, 4), np.float32))
