@@ -263,6 +263,16 @@ int32_t lwc_table_load(lwc_ctx *ctx, const float *T, const float *Q, int64_t row
 int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32_t top, const float *base,
                           const float *minw, const float *maxw, float *weights, int32_t *top_idx, float *top_sim,
                           int32_t memory);
+/* A table too large for one GPU is split by rows over n_parts contexts (ranks): each part runs lwc_table_weights on
+ * its shard and reports top_idx / top_sim; the host looks up the quality rows Q[top_idx] of its shard, all-gathers the
+ * n_parts * n_prompts * top records (any transport: they are tiny) and calls this HOST-ONLY function, which keeps the
+ * `top` best of the n_parts * top candidates per prompt (ties -> lowest global row = row_offset[part] + local row) and
+ * applies the same policy with the same arithmetic in the same order as the device path: a split table gives the
+ * bits of the unsplit one.  idx / sim: [n_parts][n_prompts][top]; q_rows: [n_parts][n_prompts][top][M] (rows of
+ * entries with idx < 0 are ignored); top_row ([n_prompts][top], global rows, -1 past the end) and top_sim may be NULL. */
+int32_t lwc_table_merge(int32_t n_parts, int32_t n_prompts, int32_t top, int32_t M, const int64_t *row_offset,
+                        const int32_t *idx, const float *sim, const float *q_rows, const float *base, const float *minw,
+                        const float *maxw, float *weights, int64_t *top_row, float *top_sim);
 
 #ifdef __cplusplus
 }

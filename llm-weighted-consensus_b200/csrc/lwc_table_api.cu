@@ -1,6 +1,9 @@
 // lwc_table_api.cu -- C ABI of the training-table weight lookup (BUILD-DEFINED, see table.cuh).
+#include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "lwc_internal.hpp"
 #include "table.cuh"
@@ -155,6 +158,68 @@ int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32
         }
     }
     if (!dev) CUDA_TRY(ctx, cudaStreamSynchronize(st)); // host results are valid on return; device results in stream order
+    return LWC_OK;
+}
+
+int32_t lwc_table_merge(int32_t n_parts, int32_t n_prompts, int32_t top, int32_t M, const int64_t *row_offset,
+                        const int32_t *idx, const float *sim, const float *q_rows, const float *base, const float *minw,
+                        const float *maxw, float *weights, int64_t *top_row, float *top_sim) {
+    // Host only: n_parts * top candidates per prompt.  Same arithmetic, in the same order, as table_weights_kernel
+    // (fmaf per neighbour in merged order; the mean of rho through the same butterfly as the kernel's warp_sum), so a
+    // table split over ranks gives the bits of the unsplit table.
+    if (n_parts < 1 || n_prompts < 0 || top < 1 || top > lwc::kTableMaxTop || M < 1 || M > LWC_MAX_VOTERS || !row_offset ||
+        !idx || !sim || !q_rows || !base || !minw || !maxw || !weights)
+        return fail(nullptr, LWC_ERR_INVALID, "lwc_table_merge: invalid argument (parts=%d prompts=%d top=%d M=%d)", n_parts,
+                    n_prompts, top, M);
+    for (int m = 0; m < M; ++m)
+        if (!(minw[m] > 0.f) || !(base[m] >= minw[m]) || !(base[m] <= maxw[m]))
+            return fail(nullptr, LWC_ERR_INVALID, "lwc_table_merge: LLM %d needs 0 < min <= base <= max", m);
+    struct Cand {
+        float sim;
+        int64_t row;
+        const float *q;
+    };
+    std::vector<Cand> cand;
+    std::vector<float> rho(M);
+    for (int p = 0; p < n_prompts; ++p) {
+        cand.clear();
+        for (int r = 0; r < n_parts; ++r)
+            for (int k = 0; k < top; ++k) {
+                const size_t at = ((size_t)r * n_prompts + p) * top + k;
+                if (idx[at] >= 0) cand.push_back({sim[at], row_offset[r] + idx[at], q_rows + at * M});
+            }
+        std::sort(cand.begin(), cand.end(),
+                  [](const Cand &a, const Cand &b) { return a.sim > b.sim || (a.sim == b.sim && a.row < b.row); });
+        const int n = (int)cand.size() < top ? (int)cand.size() : top;
+        float ssum = 0.f;
+        for (int k = 0; k < n; ++k) ssum += fmaxf(cand[k].sim, 0.f);
+        float lane_part[32] = {0.f};
+        for (int m = 0; m < M; ++m) {
+            float r = 0.f;
+            if (ssum > 0.f) {
+                for (int k = 0; k < n; ++k) r = fmaf(fmaxf(cand[k].sim, 0.f), cand[k].q[m], r);
+                r /= ssum;
+            }
+            rho[m] = r;
+        }
+        for (int lane = 0; lane < 32; ++lane) // the kernel: lane l adds rho[l], rho[32 + l], ... in that order
+            for (int j = 0; j * 32 + lane < M; ++j) lane_part[lane] += rho[j * 32 + lane];
+        for (int o = 16; o > 0; o >>= 1) { // warp_sum's xor butterfly
+            float next[32];
+            for (int l = 0; l < 32; ++l) next[l] = lane_part[l] + lane_part[l ^ o];
+            std::memcpy(lane_part, next, sizeof(next));
+        }
+        const float mean = lane_part[0] / (float)M;
+        for (int m = 0; m < M; ++m) {
+            float wv = base[m];
+            if (ssum > 0.f && mean > 0.f) wv = base[m] * (rho[m] / mean);
+            weights[(size_t)p * M + m] = fminf(fmaxf(wv, minw[m]), maxw[m]);
+        }
+        for (int k = 0; k < top; ++k) {
+            if (top_row) top_row[(size_t)p * top + k] = k < n ? cand[k].row : -1;
+            if (top_sim) top_sim[(size_t)p * top + k] = k < n ? cand[k].sim : 0.f;
+        }
+    }
     return LWC_OK;
 }
 

@@ -102,6 +102,8 @@ def load_library():
     L.lwc_table_load.restype = i32
     L.lwc_table_weights.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, i32]
     L.lwc_table_weights.restype = i32
+    L.lwc_table_merge.argtypes = [i32, i32, i32, i32] + [vp] * 10
+    L.lwc_table_merge.restype = i32
     L.lwc_stage_f64.argtypes = [vp, vp, ctypes.c_size_t, vp]
     L.lwc_stage_f64.restype = i32
     _lib = L
@@ -111,6 +113,27 @@ def load_library():
 def merge_error_codes(codes) -> int:
     arr = (ctypes.c_uint16 * max(len(codes), 1))(*codes)
     return load_library().lwc_merge_error_codes(arr, len(codes))
+
+
+def table_merge(row_offset, idx, sim, q_rows, base, minw, maxw):
+    """lwc_table_merge (host only): idx / sim [parts, prompts, top], q_rows [parts, prompts, top, M] -> weights,
+    global rows and similarities of the merged `top` neighbours."""
+    idx = np.ascontiguousarray(idx, dtype=np.int32)
+    sim = np.ascontiguousarray(sim, dtype=np.float32)
+    q_rows = np.ascontiguousarray(q_rows, dtype=np.float32)
+    off = np.ascontiguousarray(row_offset, dtype=np.int64)
+    base, minw, maxw = (np.ascontiguousarray(a, dtype=np.float32) for a in (base, minw, maxw))
+    parts, prompts, top = idx.shape
+    M = q_rows.shape[3]
+    weights = np.zeros((prompts, M), np.float32)
+    rows = np.zeros((prompts, top), np.int64)
+    sims = np.zeros((prompts, top), np.float32)
+    rc = load_library().lwc_table_merge(parts, prompts, top, M, _np_ptr(off), _np_ptr(idx), _np_ptr(sim), _np_ptr(q_rows),
+                                        _np_ptr(base), _np_ptr(minw), _np_ptr(maxw), _np_ptr(weights), _np_ptr(rows),
+                                        _np_ptr(sims))
+    if rc:
+        raise LwcError(rc, load_library().lwc_last_error_message(None).decode())
+    return weights, rows, sims
 
 
 def comm_unique_id() -> bytes:

@@ -127,4 +127,20 @@ extern "C" {
         top_sim: *mut f32,
         memory: i32,
     ) -> i32;
+    pub fn lwc_table_merge(
+        n_parts: i32,
+        n_prompts: i32,
+        top: i32,
+        M: i32,
+        row_offset: *const i64,
+        idx: *const i32,
+        sim: *const f32,
+        q_rows: *const f32,
+        base: *const f32,
+        minw: *const f32,
+        maxw: *const f32,
+        weights: *mut f32,
+        top_row: *mut i64,
+        top_sim: *mut f32,
+    ) -> i32;
 }

@@ -71,3 +71,52 @@ def test_shard_helpers_edge_cases():
     with pytest.raises(ValueError):
         shard.pool_rows(10, 0, 4)
     assert shard.max_over_ranks(None, 3.5) == 3.5
+
+
+def _table_worker(rank, world, port, out):
+    """Each rank owns a row shard of the training table; the neighbour lists (here from the f64 checker, standing in
+    for lwc_table_weights on that rank's GPU) are all-gathered and merged on every rank with lwc_table_merge."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "llm-weighted-consensus_b200"))
+    sys.path.insert(0, root)
+    import lwc_b200
+    import oracle
+    from lwc_b200 import shard
+
+    rng = np.random.default_rng(77)
+    rows, D, M, nq, top = 501, 24, 4, 5, 7
+    T = rng.standard_normal((rows, D)).astype(np.float32)
+    Q = rng.random((rows, M)).astype(np.float32)
+    q = rng.standard_normal((nq, D)).astype(np.float32)
+    base = np.ones(M, np.float32)
+    a, b = shard.request_block(rows, rank, world)  # contiguous row block of this rank
+    _, idx, sim = oracle.table_weights(T[a:b], Q[a:b], q, top, base, base * 0.5, base * 2)
+    qr = Q[a:b][np.where(idx >= 0, idx, 0)]
+    g_idx = [torch.empty((nq, top), dtype=torch.int32) for _ in range(world)]
+    g_sim = [torch.empty((nq, top), dtype=torch.float32) for _ in range(world)]
+    g_q = [torch.empty((nq, top, M), dtype=torch.float32) for _ in range(world)]
+    g_off = [torch.empty(1, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(g_idx, torch.from_numpy(idx.copy()))
+    dist.all_gather(g_sim, torch.from_numpy(sim.astype(np.float32)))
+    dist.all_gather(g_q, torch.from_numpy(qr.copy()))
+    dist.all_gather(g_off, torch.tensor([a], dtype=torch.int64))
+    w, grows, _ = lwc_b200.table_merge([int(o.item()) for o in g_off], torch.stack(g_idx).numpy(), torch.stack(g_sim).numpy(),
+                                       torch.stack(g_q).numpy(), base, base * 0.5, base * 2)
+    we, ie, _ = oracle.table_weights(T, Q, q, top, base, base * 0.5, base * 2)
+    out[rank] = {"rows_ok": bool((grows == ie).all()), "w_ok": bool(np.allclose(w, we, rtol=2e-5)), "w": w.tobytes()}
+    dist.destroy_process_group()
+
+
+def test_two_rank_table_shards_merge_to_the_unsplit_table():
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    port = 31500 + (os.getpid() % 2000)
+    mp.spawn(_table_worker, args=(world, port, out), nprocs=world, join=True)
+    assert all(out[r]["rows_ok"] and out[r]["w_ok"] for r in range(world))
+    assert out[0]["w"] == out[1]["w"]  # every rank derives the same weights

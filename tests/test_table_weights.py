@@ -178,3 +178,62 @@ def test_table_weights_device_memory_feeds_score_batch(oracle):
         ref = oracle.score_f64(E, V, w_host, oracle.SIM_COSINE)
         np.testing.assert_allclose(dconf.cpu().numpy(), ref["conf"], rtol=1e-5, atol=1e-7)
         assert ctx.lib.lwc_table_weights(ctx.handle, None, 1, 1, None, None, None, None, None, None, 7) == 400
+
+
+def shard_candidates(oracle, T, Q, q, top, base, minw, maxw, bounds):
+    """Per-shard neighbour lists as lwc_table_weights reports them (here from the f64 checker), plus Q rows."""
+    idx, sim, qr = [], [], []
+    for a, b in bounds:
+        _, i, s = oracle.table_weights(T[a:b], Q[a:b], q, top, base, minw, maxw)
+        rows = np.where(i >= 0, i, 0)
+        idx.append(i)
+        sim.append(s.astype(np.float32))
+        qr.append(Q[a:b][rows])
+    return np.stack(idx), np.stack(sim), np.stack(qr)
+
+
+def test_table_merge_of_row_shards_matches_the_unsplit_table(oracle):
+    import lwc_b200 as lwc
+    """Host-only merge (no GPU): three uneven row shards, one of them smaller than `top`."""
+    T, Q, q, base, minw, maxw = make_table(31, 700, 40, 6, 11)
+    top = 8
+    bounds = [(0, 5), (5, 400), (400, 700)]
+    idx, sim, qr = shard_candidates(oracle, T, Q, q, top, base, minw, maxw, bounds)
+    w, rows, sims = lwc.table_merge([a for a, _ in bounds], idx, sim, qr, base, minw, maxw)
+    we, ie, se = oracle.table_weights(T, Q, q, top, base, minw, maxw)
+    assert (rows == ie).all()
+    np.testing.assert_allclose(sims, se, atol=1e-6)
+    np.testing.assert_allclose(w, we, rtol=W_RTOL)
+    # ties across shards go to the lowest global row; fewer candidates than `top` leave -1 / 0
+    one = np.ones(2, np.float32)
+    idx2 = np.array([[[0, -1]], [[0, -1]]], np.int32)
+    sim2 = np.array([[[0.5, 0.0]], [[0.5, 0.0]]], np.float32)
+    w2, rows2, sims2 = lwc.table_merge([10, 3], idx2, sim2, np.ones((2, 1, 2, 2), np.float32), one, one, one)
+    assert rows2.tolist() == [[3, 10]] and sims2.tolist() == [[0.5, 0.5]]
+    idx3 = np.full((2, 1, 3), -1, np.int32)
+    idx3[1, 0, 0] = 4
+    w3, rows3, _ = lwc.table_merge([0, 100], idx3, np.full((2, 1, 3), 0.25, np.float32), np.ones((2, 1, 3, 2), np.float32),
+                                   one, one, one)
+    assert rows3.tolist() == [[104, -1, -1]]
+    with pytest.raises(lwc.LwcError):
+        lwc.table_merge([0], np.zeros((1, 1, 1), np.int32), np.zeros((1, 1, 1), np.float32), np.ones((1, 1, 1, 2), np.float32),
+                        one, 2 * one, one)
+
+
+@pytest.mark.gpu
+def test_table_split_over_two_contexts_gives_the_bits_of_the_unsplit_table():
+    import lwc_b200
+    T, Q, q, base, minw, maxw = make_table(41, 9000, 128, 5, 13)
+    top = 6
+    bounds = [(0, 3500), (3500, 9000)]
+    with lwc_b200.Context(0) as ctx:
+        ctx.table_load(T, Q)
+        w_full, i_full, s_full = ctx.table_weights(q, top, base, minw, maxw)
+        idx, sim, qr = [], [], []
+        for a, b in bounds:
+            ctx.table_load(T[a:b], Q[a:b])
+            _, i, s = ctx.table_weights(q, top, base, minw, maxw)
+            idx.append(i), sim.append(s), qr.append(Q[a:b][np.where(i >= 0, i, 0)])
+    w, rows, sims = lwc_b200.table_merge([a for a, _ in bounds], np.stack(idx), np.stack(sim), np.stack(qr), base, minw, maxw)
+    assert (rows == i_full).all() and (sims == s_full).all()
+    assert (w == w_full).all()
