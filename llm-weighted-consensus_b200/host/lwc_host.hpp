@@ -217,6 +217,27 @@ class Context {
         if (rc) throw error::ResponseError((uint16_t)rc, lwc_last_error_message(ctx_));
     }
 
+    // Training-table weights: what a weight::Fetcher<CTX, TrainingTableData> implementation computes
+    // (weight.rs:66-74,99-117; build-defined policy, see include/lwc_b200.h).
+    struct TableLimits {
+        std::vector<float> base, min, max; // per LLM: base_weight / min_weight / max_weight (llm/mod.rs:663-688)
+    };
+    void table_load(const std::vector<float> &T, const std::vector<float> &Q, int64_t rows, int D, int M) const {
+        if ((int64_t)T.size() != rows * D || (int64_t)Q.size() != rows * M) throw error::ResponseError(400, "table shape");
+        check(lwc_table_load(ctx_, T.data(), Q.data(), rows, D, M));
+    }
+    // one weight per LLM for each of the n prompt embeddings in q [n][D]
+    std::vector<float> table_weights(const std::vector<float> &q, int n, int top, const TableLimits &lim,
+                                     std::vector<int32_t> *top_idx = nullptr, std::vector<float> *top_sim = nullptr) const {
+        const size_t M = lim.base.size();
+        std::vector<float> w((size_t)n * M);
+        if (top_idx) top_idx->assign((size_t)n * top, -1);
+        if (top_sim) top_sim->assign((size_t)n * top, 0.f);
+        check(lwc_table_weights(ctx_, q.data(), n, top, lim.base.data(), lim.min.data(), lim.max.data(), w.data(),
+                                top_idx ? top_idx->data() : nullptr, top_sim ? top_sim->data() : nullptr, LWC_MEM_HOST));
+        return w;
+    }
+
   private:
     lwc_ctx *ctx_ = nullptr;
 };

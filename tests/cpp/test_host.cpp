@@ -246,6 +246,31 @@ static int gpu_checks() {
         }
         REQUIRE(tl.winner == 2 && tl.rank[0] == 2);
     }
+    // training-table weights through the host wrapper: the prompt equal to table row 5 has row 5 as its first
+    // neighbour with cosine 1, and an all-equal quality table returns the base weights
+    {
+        const int rows = 64, D = 32, M = 3;
+        std::mt19937 g(9);
+        std::normal_distribution<float> nd;
+        std::vector<float> T((size_t)rows * D), Q((size_t)rows * M, 0.5f), q(D);
+        for (auto &x : T) x = nd(g);
+        for (int k = 0; k < D; ++k) q[k] = 2.0f * T[5 * D + k];
+        const Context &c = batcher.context();
+        c.table_load(T, Q, rows, D, M);
+        Context::TableLimits lim{{1.0f, 2.0f, 3.0f}, {0.5f, 1.0f, 1.5f}, {2.0f, 4.0f, 6.0f}};
+        std::vector<int32_t> idx;
+        std::vector<float> sim;
+        const std::vector<float> w = c.table_weights(q, 1, 4, lim, &idx, &sim);
+        REQUIRE(idx[0] == 5 && std::fabs(sim[0] - 1.0f) < 1e-6f);
+        for (int m = 0; m < M; ++m) REQUIRE(std::fabs(w[m] - lim.base[m]) < 1e-6f);
+        try {
+            lim.min[0] = 5.0f; // min > base: the reference's validate() refuses it (llm/mod.rs:671-687)
+            c.table_weights(q, 1, 4, lim);
+            REQUIRE(false);
+        } catch (const error::ResponseError &e) {
+            REQUIRE(e.code == 400);
+        }
+    }
     // argument errors surface as ResponseError 400, like Error::ExpectedTwoOrMoreChoices would
     try {
         Request bad;
