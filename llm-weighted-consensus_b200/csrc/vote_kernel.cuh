@@ -87,16 +87,25 @@ __global__ void __launch_bounds__(kVoteRows) vote_tile_kernel(const float *__res
                 s += pk;
             }
         }
-        if (s > 0.f) {
-            const float inv = 1.0f / s;
-            for (int j = 0; j < n_choices; ++j) o[j] *= inv; // client.rs:1789-1791
-        } else { // unreachable!() in the reference (client.rs:1786-1788): mark the voter absent
-            for (int j = 0; j < n_choices; ++j) o[j] = __int_as_float(0x7fc00000);
+        // normalise (client.rs:1789-1791) and write the row out from this thread: consecutive threads own
+        // consecutive rows, so a warp's stores cover one contiguous span (no index arithmetic per element)
+        const bool ok = s > 0.f; // else unreachable!() in the reference (client.rs:1786-1788): mark the voter absent
+        const float inv = ok ? 1.0f / s : 0.f;
+        const float nanv = __int_as_float(0x7fc00000);
+        float *out = V + (size_t)(row0 + threadIdx.x) * n_choices;
+        if ((n_choices & 3) == 0 && (reinterpret_cast<uintptr_t>(V) & 15u) == 0) {
+            for (int j = 0; j < n_choices; j += 4) {
+                float4 r4;
+                r4.x = ok ? o[j] * inv : nanv;
+                r4.y = ok ? o[j + 1] * inv : nanv;
+                r4.z = ok ? o[j + 2] * inv : nanv;
+                r4.w = ok ? o[j + 3] * inv : nanv;
+                *reinterpret_cast<float4 *>(out + j) = r4;
+            }
+        } else {
+            for (int j = 0; j < n_choices; ++j) out[j] = ok ? o[j] * inv : nanv;
         }
     }
-    __syncthreads();
-    float *out = V + (size_t)row0 * n_choices;
-    for (int i = threadIdx.x; i < rows * n_choices; i += kVoteRows) out[i] = out_s[(i / n_choices) * pitch + i % n_choices];
 }
 
 } // namespace lwc
