@@ -203,8 +203,11 @@ int32_t lwc_pool_consensus(lwc_ctx *ctx, const lwc_pool_desc *desc, const float 
  * with this call.  It is lwc_pool_consensus for a single GPU with every pointer in DEVICE memory
  * (desc->memory must be LWC_MEM_DEVICE, no communicator attached, `winner` is a device int64), and it
  * takes its working memory from a fixed array that lives inside the library's device image instead of
- * from cudaMalloc: LWC_STATIC_SCRATCH_BYTES per GPU, held from the moment the library is loaded on
- * that GPU until the process exits, whether or not this function is ever called.
+ * from cudaMalloc: LWC_STATIC_SCRATCH_BYTES per GPU, held from the moment the library's pool module is
+ * loaded on that GPU until the process exits.  CUDA loads modules lazily by default, so that moment is
+ * the first pool call on the GPU -- at the latest the first call of this function.  A host that is about
+ * to hand ALL of a GPU's memory to its own pool must therefore make one warm-up call of this function
+ * on that GPU first (or run with CUDA_MODULE_LOADING=EAGER); afterwards no call needs memory.
  *   Limits: N <= LWC_STATIC_POOL_MAX_ROWS and N * D <= LWC_STATIC_POOL_MAX_ELEMS; anything larger is
  *   refused with 400 and a message naming the limit (use lwc_pool_consensus then).
  *   The call makes no cudaMalloc/cudaFree or other allocating call.  It is asynchronous on `stream`

@@ -31,6 +31,7 @@ int fail(lwc_ctx *ctx, int code, const char *fmt, ...) {
     vsnprintf(buf, sizeof buf, fmt, ap);
     va_end(ap);
     if (ctx) {
+        std::lock_guard<std::mutex> lk(ctx->err_mu);
         ctx->err = buf;
     } else {
         std::lock_guard<std::mutex> lk(g_err_mu);
@@ -399,9 +400,15 @@ extern "C" {
 const char *lwc_version(void) { return LWC_VERSION_STRING; }
 
 const char *lwc_last_error_message(const lwc_ctx *ctx) {
-    if (ctx) return ctx->err.c_str();
+    // The text is copied under the lock that failing calls hold while they write it, into storage owned by the
+    // asking thread: the pointer stays valid until this thread asks again, whatever other threads do meanwhile.
     static thread_local std::string copy;
-    copy = lwc_host::last_create_error();
+    if (ctx) {
+        std::lock_guard<std::mutex> lk(ctx->err_mu);
+        copy = ctx->err;
+    } else {
+        copy = lwc_host::last_create_error();
+    }
     return copy.c_str();
 }
 

@@ -33,6 +33,7 @@ struct lwc_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;
     std::mutex mu;
+    mutable std::mutex err_mu; // guards `err` alone: lwc_last_error_message may run while another thread's call fails
     std::string err;
     uint64_t launches = 0;
     lwc_host::Slot slots[2];

@@ -61,8 +61,27 @@ NcclApi &nccl_api() {
                         __FILE__, __LINE__);                                                                     \
     } while (0)
 
+// Drops the fused-gather state: this rank's mappings of its peers' buffers are closed and later calls use the
+// NCCL all-gather until the caller exports and attaches again.
+void p2p_detach(lwc_ctx *ctx) {
+    for (auto &m : ctx->p2p_mapped)
+        for (auto &q : m)
+            if (q) {
+                cudaIpcCloseMemHandle(q);
+                q = nullptr;
+            }
+    ctx->p2p_ready = false;
+    ctx->p2p_n_own = 0;
+    ctx->p2p_D = 0;
+}
+
 int pool_ensure(lwc_ctx *ctx, int which, size_t bytes) {
     if (bytes <= ctx->pool_cap[which]) return LWC_OK;
+    // Slots 0 and 1 are the buffers lwc_pool_p2p_export handed to the peers.  Growing one frees the memory their
+    // mappings point at, so the fused route ends here -- on every rank at the same call, because the ranks of a
+    // communicator call lwc_pool_consensus with the same shape (the peers have long finished reading: the previous
+    // call's closing collectives follow every rank's tensor pass).
+    if (which < 2 && ctx->pool_buf[which] && ctx->p2p_n_own != 0) p2p_detach(ctx);
     if (ctx->pool_buf[which]) CUDA_TRY(ctx, cudaFree(ctx->pool_buf[which]));
     ctx->pool_buf[which] = nullptr;
     ctx->pool_cap[which] = 0;
@@ -102,7 +121,8 @@ int pool_run(lwc_ctx *ctx, const PoolScratch &sc, const float *dE, const float *
              int M, cudaStream_t st) {
     const int nranks = ctx->comm ? ctx->nranks : 1, rank = ctx->comm ? ctx->rank : 0;
     const long long n_total = n_own * nranks, row0 = n_own * rank;
-    NcclApi &nc = nccl_api();
+    static NcclApi no_nccl;                              // never called: every use below is under nranks > 1
+    NcclApi &nc = nranks > 1 ? nccl_api() : no_nccl;     // a single-GPU call must not dlopen NCCL
     // 1. normalise own rows (bf16) + tally vector
     {
         const int warps = 8;
@@ -270,10 +290,15 @@ int32_t lwc_pool_p2p_attach(lwc_ctx *ctx, const void *all_handles) {
         return fail(ctx, LWC_ERR_INVALID, "lwc_pool_p2p_attach: call lwc_comm_init and lwc_pool_p2p_export first");
     if (ctx->nranks > 64) return fail(ctx, LWC_ERR_INVALID, "lwc_pool_p2p_attach: at most 64 ranks");
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    NcclApi &nc = nccl_api();
+    // device block: peer_ehat[64], peer_t[64], shard_done[64], one agreement word
+    const size_t flag_off = 2 * 64 * sizeof(void *) + 64 * sizeof(unsigned);
+    if (!ctx->p2p_dev) CUDA_TRY(ctx, cudaMalloc(&ctx->p2p_dev, flag_off + 64));
     const char *hp = static_cast<const char *>(all_handles);
     void *host_ptrs[2 * 64] = {nullptr};
-    for (int r = 0; r < ctx->nranks; ++r) {
-        for (int k = 0; k < 2; ++k) {
+    int local_ok = ctx->no_p2p ? 0 : 1, local_rc = LWC_OK;
+    for (int r = 0; r < ctx->nranks && local_ok; ++r) {
+        for (int k = 0; k < 2 && local_ok; ++k) {
             void *ptr = ctx->pool_buf[k];
             if (r != ctx->rank) {
                 if (ctx->p2p_mapped[r][k]) {
@@ -282,17 +307,37 @@ int32_t lwc_pool_p2p_attach(lwc_ctx *ctx, const void *all_handles) {
                 }
                 cudaIpcMemHandle_t h;
                 memcpy(&h, hp + (size_t)r * 128 + k * 64, 64);
-                CUDA_TRY(ctx, cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+                const cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+                if (e != cudaSuccess) {
+                    cudaGetLastError();
+                    local_ok = 0;
+                    local_rc = fail(ctx, LWC_ERR_INTERNAL, "lwc_pool_p2p_attach: cudaIpcOpenMemHandle(rank %d) failed: %s", r,
+                                    cudaGetErrorString(e));
+                    break;
+                }
                 ctx->p2p_mapped[r][k] = ptr;
             }
             host_ptrs[k * 64 + r] = ptr;
         }
     }
-    if (!ctx->p2p_dev) CUDA_TRY(ctx, cudaMalloc(&ctx->p2p_dev, 2 * 64 * sizeof(void *) + 64 * sizeof(unsigned)));
+    // The route is chosen per call from this state, and the two routes issue different collectives: every rank must
+    // hold the same answer.  So the ranks agree here (min over "my mappings are open and LWC_POOL_NO_P2P is unset");
+    // a rank whose attach failed still takes part, then reports its error.
+    int *flag_d = reinterpret_cast<int *>(static_cast<char *>(ctx->p2p_dev) + flag_off);
+    int agreed = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->p2p_dev, host_ptrs, sizeof host_ptrs, cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(flag_d, &local_ok, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    NCCL_TRY(ctx, nc.AllReduce(flag_d, flag_d, 1, ncclInt32, ncclMin, ctx->comm, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&agreed, flag_d, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    ctx->p2p_ready = true;
-    return LWC_OK;
+    ctx->p2p_ready = agreed != 0;
+    if (!ctx->p2p_ready) { // some rank cannot use the fused route: nobody does
+        const long long n_own = ctx->p2p_n_own;
+        const int D = ctx->p2p_D;
+        p2p_detach(ctx);
+        ctx->p2p_n_own = n_own, ctx->p2p_D = D; // the export stays valid for another attach
+    }
+    return local_rc;
 }
 
 int32_t lwc_pool_consensus(lwc_ctx *ctx, const lwc_pool_desc *desc, const float *E, const float *V, const float *w,

@@ -44,12 +44,21 @@ struct SmallCfg {
     static constexpr int PITCH = NT + 1;
     // fragment registers per lane that cross warps in the K-split reduction
     static constexpr int NACC = (MT * NTL + (X3 ? MT * NTL : 0)) * 4;
+    // HH fragment registers per lane that are actually accumulated (upper blocks of the symmetric tile)
+    static constexpr int NHH = (MT == 1 ? NTL : NTL + (NTL - 2)) * 4;
     static constexpr size_t smem_bytes() {
         size_t red = (size_t)(KW - 1) * NACC * 32 * sizeof(float);
         size_t tile = (size_t)NT * PITCH * sizeof(float);
-        return red + tile;
+        size_t flush = X3 ? (size_t)KW * NHH * 32 * sizeof(float) : 0;
+        return red + tile + flush;
     }
 };
+
+// The tensor core's fp32 accumulator truncates when it aligns addends (measured on this part: ~1.1e-8 relative
+// drift per accumulated MMA on same-sign sums such as the diagonal |E_i|^2), so an fp32-grade route must not let
+// one accumulator run through a whole long row: after this many MMAs the running sums are moved out with
+// ordinary round-to-nearest adds and the accumulators restart.
+constexpr int kMmaChain = 64;
 
 template <int NT, bool X3, int KW, int U>
 __global__ void __launch_bounds__(KW * 32, (NT == 16 ? 32 : 16) / KW)
@@ -59,6 +68,7 @@ score_small_kernel(const ScoreParams p) {
     extern __shared__ __align__(16) float smem[];
     float *red = smem;                                    // [KW-1][NACC][32]
     float *tile = smem + (size_t)(KW - 1) * C::NACC * 32; // [NT][PITCH]
+    float *fl = tile + NT * PITCH + (size_t)(threadIdx.x >> 5) * C::NHH * 32 + (threadIdx.x & 31); // X3: [KW][NHH][32], lane-private
 
     const int r = blockIdx.x;
     const int lane = threadIdx.x & 31;
@@ -87,6 +97,12 @@ score_small_kernel(const ScoreParams p) {
         }
         // 16-wide chunks, dealt round-robin in groups of U to the KW warps
         const int nchunk = (D + 15) >> 4;
+        constexpr int kFlushIters = kMmaChain / (2 * U) > 0 ? kMmaChain / (2 * U) : 1; // 2 MMAs per accumulator and chunk
+        int since = 0;
+        if (X3) {
+#pragma unroll
+            for (int s = 0; s < C::NHH; ++s) fl[s * 32] = 0.f;
+        }
         for (int c0 = warp * U; c0 < nchunk; c0 += KW * U) {
             float4 buf[U][RPL];
 #pragma unroll
@@ -131,6 +147,33 @@ score_small_kernel(const ScoreParams p) {
                     }
                 }
             }
+            if (X3 && ++since == kFlushIters) { // bound the in-accumulator chain (HL is ~2^-11 of HH: its drift is harmless)
+                since = 0;
+                int s = 0;
+#pragma unroll
+                for (int a = 0; a < MT; ++a)
+#pragma unroll
+                    for (int b = 0; b < NTL; ++b)
+                        if (b >= 2 * a) {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                fl[s * 32] += hh[a][b][e];
+                                hh[a][b][e] = 0.f;
+                                ++s;
+                            }
+                        }
+            }
+        }
+        if (X3) {
+            int s = 0;
+#pragma unroll
+            for (int a = 0; a < MT; ++a)
+#pragma unroll
+                for (int b = 0; b < NTL; ++b)
+                    if (b >= 2 * a) {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) hh[a][b][e] += fl[(s++) * 32];
+                    }
         }
 
         // ---- K-split reduction: warps 1..KW-1 park their fragments, warp 0 adds them in order

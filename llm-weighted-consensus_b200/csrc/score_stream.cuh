@@ -203,9 +203,19 @@ score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
 
         const int cpw = ((KS >> 4) + NCW - 1) / NCW; // chunks of a full stage owned by one consumer
         const int c_lo = cw * cpw;
+        // X3: running sums of HH moved out of the tensor-core accumulators every few stages (kMmaChain, score_small.cuh)
+        float fh[MT][NTL][4];
+#pragma unroll
+        for (int a = 0; a < MT; ++a)
+#pragma unroll
+            for (int b = 0; b < NTL; ++b)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) fh[a][b][e] = 0.f;
+        const int flush_stages = max(1, kMmaChain / (2 * cpw)); // 2 MMAs per accumulator and chunk
         int slot = 0;
         uint32_t phase = 0;
         for (int q = 0; q < nreq; ++q) {
+            int since = 0;
             for (int s = 0; s < spr; ++s) {
                 mbar_wait(full0 + 8 * slot, phase);
                 const int kv = min(KS, D - s * KS);        // valid columns of this stage
@@ -255,6 +265,33 @@ score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
                     slot = 0;
                     phase ^= 1u;
                 }
+                if (X3 && ++since == flush_stages && s + 1 < spr) {
+                    since = 0;
+#pragma unroll
+                    for (int a = 0; a < MT; ++a)
+#pragma unroll
+                        for (int b = 0; b < NTL; ++b)
+                            if (b >= 2 * a) {
+#pragma unroll
+                                for (int e = 0; e < 4; ++e) {
+                                    fh[a][b][e] += hh[a][b][e];
+                                    hh[a][b][e] = 0.f;
+                                }
+                            }
+                }
+            }
+            if (X3) {
+#pragma unroll
+                for (int a = 0; a < MT; ++a)
+#pragma unroll
+                    for (int b = 0; b < NTL; ++b)
+                        if (b >= 2 * a) {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                hh[a][b][e] += fh[a][b][e];
+                                fh[a][b][e] = 0.f;
+                            }
+                        }
             }
             // ---- request end: park this warp's partial fragments (buffer free once q-1 was drained)
             mbar_wait(redempty, ((uint32_t)q & 1u) ^ 1u);

@@ -374,6 +374,10 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                 uint32_t z[32];
 #pragma unroll
                 for (int e = 0; e < 32; ++e) z[e] = 0u;
+                // the accumulator this request's even chunks use: with an odd chunk count it alternates from request
+                // to request, and the two Y halves are added below in chunk-parity order (even chunks' first) so
+                // that a request's bits do not depend on its position in the batch
+                const uint32_t first_ab = tile & 1u;
                 for (int ch = 0; ch < nchunk; ++ch, ++tile) {
                     const uint32_t ab = tile & 1u;
                     mbar_wait_backoff(tfull0 + 8 * ab, (tile >> 1) & 1u, 200);
@@ -400,8 +404,9 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                 const uint32_t last_ab = (tile - 1u) & 1u;
                 float yd = 0.f;
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    tmem_ld32(lane_addr + (uint32_t)h * 256u + 128u + (uint32_t)(ew * 32), v);
+                for (int hh = 0; hh < 2; ++hh) {
+                    const uint32_t h = (uint32_t)hh ^ first_ab;
+                    tmem_ld32(lane_addr + h * 256u + 128u + (uint32_t)(ew * 32), v);
 #pragma unroll
                     for (int e = 0; e < 32; ++e) yd += (lane == e) ? v[e] : 0.f;
                 }
@@ -418,8 +423,8 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                 for (int c = 0; c < 4; ++c) {
                     float cs = 0.f;
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const uint32_t ya = lane_addr + (uint32_t)h * 256u + 128u + (uint32_t)(c * 32);
+                    for (int hh = 0; hh < 2; ++hh) {
+                        const uint32_t ya = lane_addr + ((uint32_t)hh ^ first_ab) * 256u + 128u + (uint32_t)(c * 32);
                         tmem_ld32(ya, v);
                         tmem_st32(ya, z);
 #pragma unroll

@@ -50,6 +50,25 @@ def main():
     for k in ("conf", "cw", "agree"):
         assert np.array_equal(got[k], got2[k], equal_nan=True), k
 
+    # Growing the exported buffers frees what the peers have mapped: a larger pool must end the fused route on
+    # every rank (NCCL all-gather from then on), and the first shape must still score correctly afterwards.
+    Eb = np.concatenate([Eo, Eo[::-1]])
+    Vb = np.concatenate([Vo, Vo[:, ::-1]], axis=1)
+    big = ctx.pool_consensus(Eb, Vb, w)
+    sums = [None] * world
+    dist.all_gather_object(sums, float(big["conf"].sum()))
+    assert abs(sum(sums) - 1.0) < 1e-3, sums
+    after = ctx.pool_consensus(Eo, Vo, w)
+    for k in ("conf", "cw", "agree"):
+        assert np.array_equal(after[k], got_nccl[k], equal_nan=True), ("after growth: not the NCCL route's bits", k)
+    # export + attach again: the fused route is back and gives its earlier bits
+    mine = ctx.pool_p2p_export(Eo.shape[0], D)
+    dist.all_gather_object(handles, mine)
+    ctx.pool_p2p_attach(b"".join(handles))
+    again = ctx.pool_consensus(Eo, Vo, w)
+    for k in ("conf", "cw", "agree"):
+        assert np.array_equal(again[k], got[k], equal_nan=True), ("re-attached fused route", k)
+
     # every rank must hold identical winner/agree; conf slices reassemble to the whole
     conf_parts = [None] * world
     dist.all_gather_object(conf_parts, got["conf"])

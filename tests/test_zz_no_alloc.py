@@ -7,7 +7,10 @@ image, so the only memory this test allocates is what ANY caller brings: the inp
 
 The check: through the C ABI, on two calls in a row (the second smaller, so stale data from the first
 is still lying in the shared array), the results must match lwc_pool_consensus -- the existing,
-allocating entry point -- within the bf16 tolerance the pool tests use, and the winner must be the same.
+allocating entry point.  Both run the same kernels in the same order on one GPU, so the match is required
+to be BIT-EXACT (a stale word read from the shared array would show up as a differing bit long before it
+exceeded a tolerance); the CPU oracle is compared as well, within the bf16 tolerance the pool tests use.
+The second call must also leave the device's free memory where it was: nothing is allocated.
 This file sorts last on purpose: if it fails, `pytest -x` has already run everything else.
 """
 import ctypes
@@ -60,7 +63,15 @@ def _run(ctx, lwc, entry, E, V, w):
             b.free()
 
 
-def test_static_scratch_entry_matches_the_allocating_one_twice_in_a_row():
+def _free_bytes():
+    """Free device memory as the CUDA runtime reports it (cudaMemGetInfo), read through torch."""
+    import torch
+
+    torch.cuda.synchronize()
+    return torch.cuda.mem_get_info(0)[0]
+
+
+def test_static_scratch_entry_matches_the_allocating_one_twice_in_a_row(oracle):
     import lwc_b200 as lwc
 
     with lwc.Context(device=0) as ctx:
@@ -69,13 +80,45 @@ def test_static_scratch_entry_matches_the_allocating_one_twice_in_a_row():
             E, V, w = _pool(N, D, M, seed)
             want = _run(ctx, lwc, ctx.lib.lwc_pool_consensus, E, V, w)
             got = _run(ctx, lwc, ctx.lib.lwc_pool_consensus_static, E, V, w)
-            top = float(np.max(np.abs(want["conf"])))
-            assert top > 0
-            assert np.max(np.abs(got["conf"] - want["conf"])) <= BF16_TOL * top
-            assert np.max(np.abs(got["cw"] - want["cw"])) <= BF16_TOL * float(np.max(np.abs(want["cw"])))
-            np.testing.assert_allclose(got["agree"], want["agree"], rtol=BF16_TOL, atol=BF16_TOL * top)
+            for k in ("conf", "cw", "agree"):
+                assert np.array_equal(got[k], want[k], equal_nan=True), k
             assert got["winner"] == want["winner"]
+            ref = oracle.pool_f64(E, V, w, method=0)
+            top = float(np.max(np.abs(ref["conf"])))
+            assert top > 0
+            assert np.max(np.abs(got["conf"] - ref["conf"])) <= BF16_TOL * top
+            assert np.max(np.abs(got["cw"] - ref["cw"])) <= BF16_TOL * float(np.max(np.abs(ref["cw"])))
+            np.testing.assert_allclose(got["agree"], ref["agree"], rtol=BF16_TOL, atol=BF16_TOL * top)
+            assert got["winner"] == ref["winner"]
             assert abs(float(got["conf"].sum()) - 1.0) < 1e-3
+
+
+def test_static_scratch_entry_allocates_nothing():
+    """With the caller's buffers already in place, a (second) call must not move the device's free memory."""
+    import lwc_b200 as lwc
+
+    with lwc.Context(device=0) as ctx:
+        N, D, M = 2048, 256, 4
+        E, V, w = _pool(N, D, M, 9)
+        bufs = [lwc.DeviceBuffer(ctx, n) for n in (E.nbytes, V.nbytes, w.nbytes, 4 * N, 4 * N, 4 * M, 8)]
+        try:
+            for b, a in zip(bufs, (E, V, w)):
+                b.upload(a)
+            desc = lwc.PoolDesc(N, D, M, lwc.PREC_BF16, lwc.MEM_DEVICE)
+            args = [ctypes.c_void_p(b.ptr) for b in bufs]
+
+            def call():
+                rc = ctx.lib.lwc_pool_consensus_static(ctx.handle, ctypes.byref(desc), *args, None)
+                assert rc == 0, ctx.lib.lwc_last_error_message(ctx.handle).decode()
+                ctx.synchronize()
+
+            call()  # the first call on a device resolves the array's address (and loads the module)
+            before = _free_bytes()
+            call()
+            assert _free_bytes() == before
+        finally:
+            for b in bufs:
+                b.free()
 
 
 def test_static_scratch_entry_refuses_what_does_not_fit():
