@@ -19,6 +19,13 @@ With N > 1 (launched under torchrun, one rank per GPU) every rank scores its own
             against the measured HBM copy bandwidth in MEASURED_PEAKS.json.
   cpu_baseline  the oracle's reference-typed port (Decimal tally + f64 embeddings) on all host
             cores, timed on a bounded sample (rank 0, N = 1 only).
+  parity_sample a 256-request sample of the timed launch's own outputs against the f64 oracle.
+  cfg1      BASELINE.json configs[0] literally: ONE request, single thread, on the CPU port
+            (cpu_baseline_cfg1) and through lwc_score_batch(LWC_MEM_HOST) on the GPU (gpu_cfg1).
+  extra     the other BASELINE.json configs in the same record: cfg3 (65,536 x 32 x 3072, sharded by
+            request over the N ranks, strong scaling), cfg5's pool shape (32,768 x N rows x 1024,
+            rows sharded, NCCL all-gather route and the gather fused into the tensor kernel), and at
+            N = 1 cfg4 (8,192 x 128 x 3072 on tcgen05), each with its own parity check.
 PyTorch is used only for events/streams bookkeeping and the torch.distributed barrier.
 """
 import argparse
@@ -167,38 +174,132 @@ def cpu_baseline(E, V, w, budget_s=10.0):
                       f"({total_s:.1f} s of compute; Decimal tally + f64 Gram, OpenMP over requests)"}
 
 
+def workload_string(R, N, D, M):
+    """The same string in both arms: the driver compares config.workload to decide whether they ran the same thing."""
+    return f"{WORKLOAD}: {R} requests x {N} candidates x {D}-dim fp32, {M} voters, per GPU"
+
+
+def cfg1_cpu(reps=2000):
+    """BASELINE.json configs[0] literally: one request (16 x 1536, 4 weighted voters) on ONE thread -- the reference
+    runs its tally on one task (client.rs:384-456) -- Decimal tally + f64 normalise/Gram/vote, per-call compute time."""
+    import oracle
+    from lwc_b200 import synth
+
+    R, N, D, M = synth.CONFIGS["cfg1"]
+    E, V, w, _ = synth.make_batch(R, N, D, M, seed=0x5EED0001, edge_cases=False)
+    for _ in range(50):
+        oracle.score_port(E, V, w, oracle.SIM_COSINE, nthreads=1)
+    ns = np.array([oracle.score_port(E, V, w, oracle.SIM_COSINE, nthreads=1)["seconds"] for _ in range(reps)]) * 1e9
+    return {"median_ns": float(np.median(ns)), "p99_ns": float(np.percentile(ns, 99)), "min_ns": float(ns.min()), "reps": reps,
+            "threads": 1, "kind": "port", "what": "1 request, 16 x 1536, 4 voters: Decimal tally + f64 Gram, compute phase of one call"}
+
+
 def run_reference(args):
-    """--impl reference: the CPU port of the reference path, all host threads, same config."""
+    """--impl reference: the CPU port of the reference path, all host threads, the product arm's config: every step
+    scores the full batch."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    # before the OpenMP runtime starts: one thread per core, neighbours close (step times varied 2x without it)
+    os.environ.setdefault("OMP_PROC_BIND", "close")
+    os.environ.setdefault("OMP_PLACES", "cores")
     import oracle
     from lwc_b200 import synth
 
     R, N, D, M = synth.CONFIGS[WORKLOAD]
-    sample = min(R, 1024)
-    E, V, w, _ = synth.make_batch(sample, N, D, M)
+    E, V, w, _ = synth.make_batch(R, N, D, M)
     cores = host_cores()
     for _ in range(args.warmup):
         oracle.score_port(E, V, w, oracle.SIM_COSINE, nthreads=cores)
-    secs = [oracle.score_port(E, V, w, oracle.SIM_COSINE, nthreads=cores)["seconds"] for _ in range(args.steps)]
+    secs = np.array([oracle.score_port(E, V, w, oracle.SIM_COSINE, nthreads=cores)["seconds"] for _ in range(args.steps)])
     total = float(np.sum(secs))
-    value = sample * args.steps / total
+    value = R * args.steps / total
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64+decimal96",
         "data": "synthetic",
-        "config": {"workload": f"{WORKLOAD}: {R} requests x {N} candidates x {D}-dim, {M} voters",
-                   "step": f"bounded sample: first {sample} requests of the batch per step"},
+        "config": {"workload": workload_string(R, N, D, M), "step": f"the full batch of {R} requests per step"},
+        "step_ms": {"min": float(secs.min() * 1e3), "median": float(np.median(secs) * 1e3), "max": float(secs.max() * 1e3)},
+        "value_at_median_step": R / float(np.median(secs)),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{args.steps} steps x {sample} requests; the Rust reference cannot be built "
+                         "sample": f"{args.steps} steps x {R} requests (the whole batch), OMP_PROC_BIND="
+                                   f"{os.environ.get('OMP_PROC_BIND')}; the Rust reference cannot be built "
                                    "here (no cargo/rustc), so this is the C restatement in oracle/"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "cpu_baseline_cfg1": cfg1_cpu(),
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
     return 0
+
+
+def parity_sample(oracle_mod, E, V, w, got, rtol=1e-5, atol=1e-7):
+    """A sample of the timed launch's own outputs against the f64 oracle (checker only; runs after the timed
+    regions).  tolerance_used = max |got - want| / (rtol |want| + atol): <= 1 means the stated bar holds."""
+    want = oracle_mod.score_f64(E, V, w, oracle_mod.SIM_COSINE)
+    err = np.abs(got["conf"].astype(np.float64) - want["conf"])
+    top = np.maximum(np.abs(want["conf"]).max(axis=1, keepdims=True), 1e-30)
+    scored = want["winner"] >= 0
+    # a winner is "the same" when it is the oracle's, or the oracle cannot separate the two (gap below fp32 resolution)
+    same = got["winner"] == want["winner"]
+    rows = np.arange(len(same))
+    gw = np.where(got["winner"] >= 0, got["winner"], 0)
+    near = scored & (got["winner"] >= 0) & (np.abs(want["conf"][rows, gw] - want["conf"].max(axis=1)) <= 2e-6 * top[:, 0])
+    return {"requests": int(len(same)), "max_rel_conf_err": float(np.max(err / np.maximum(np.abs(want["conf"]), 1e-30) *
+                                                                           (np.abs(want["conf"]) > 1e-3 * top))),
+            "max_conf_err_over_top": float(np.max(err / top)),
+            "tolerance_used": float(np.max(err / (rtol * np.abs(want["conf"]) + atol))),
+            "tolerance": {"rtol": rtol, "atol": atol},
+            "winner_agreement": float(np.mean(same | near)), "winner_exact": float(np.mean(same))}
+
+
+def h2d_peak(torch, nbytes, reps=5):
+    """Plain pinned cudaMemcpyAsync host->device rate of this box (best of `reps`), the ceiling of any host-memory path."""
+    src = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    dst = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    best = 0.0
+    for _ in range(reps + 1):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        dst.copy_(src, non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize()
+        best = max(best, nbytes / (e0.elapsed_time(e1) * 1e-3) / 1e9)
+    del src, dst
+    return best
+
+
+def cfg1_gpu(ctx, lwc_b200, synth, reps=2000):
+    """configs[0] on the GPU: the latency ONE request pays through lwc_score_batch(LWC_MEM_HOST) -- pinned buffers,
+    H2D, one launch, D2H, stream synchronise -- wall clock around the C call."""
+    import ctypes
+
+    R, N, D, M = synth.CONFIGS["cfg1"]
+    E, V, w, _ = synth.make_batch(R, N, D, M, seed=0x5EED0001, edge_cases=False)
+    hb = [lwc_b200.HostBuffer(ctx, a.shape, np.float32) for a in (E, V, w)]
+    for b, a in zip(hb, (E, V, w)):
+        b.array[...] = a
+    outs = [lwc_b200.HostBuffer(ctx, sh, t) for sh, t in (((R, N), np.float32), ((R, N), np.float32), ((R, M), np.float32),
+                                                           ((R,), np.int32), ((R, N), np.int32))]
+    desc = lwc_b200.BatchDesc(R, N, D, M, lwc_b200.SIM_COSINE, lwc_b200.PREC_FP32, lwc_b200.MEM_HOST, 1)
+    vp = ctypes.c_void_p
+    argv = (ctx.handle, ctypes.byref(desc), *[vp(b.ptr) for b in hb], *[vp(o.ptr) for o in outs], None)
+    fn = ctx.lib.lwc_score_batch
+    for _ in range(100):
+        fn(*argv)
+    us = np.empty(reps)
+    for i in range(reps):
+        t0 = time.perf_counter_ns()
+        rc = fn(*argv)
+        us[i] = (time.perf_counter_ns() - t0) * 1e-3
+        if rc:
+            raise lwc_b200.LwcError(rc, ctx.lib.lwc_last_error_message(ctx.handle).decode())
+    winner = int(outs[3].array[0])
+    for b in hb + outs:
+        b.free()
+    return {"median_us": float(np.median(us)), "p99_us": float(np.percentile(us, 99)), "min_us": float(us.min()), "reps": reps,
+            "api": "lwc_score_batch(LWC_MEM_HOST), 1 request, pinned buffers, blocking", "winner": winner}
 
 
 def run_b200(args):
@@ -255,20 +356,17 @@ def run_b200(args):
     desc_host = lwc_b200.BatchDesc(R, N, D, M, lwc_b200.SIM_COSINE, lwc_b200.PREC_FP32, lwc_b200.MEM_HOST, 1)
     stream = torch.cuda.Stream()
 
-    # the timed loop calls the C entry point with pre-built arguments: the launches have to stay ahead of a
-    # 62 us kernel for consecutive launches to overlap, so nothing is re-wrapped per step
-    import ctypes
-    _vp = ctypes.c_void_p
-    _fn = ctx.lib.lwc_score_batch
-    _dev_args = [(ctx.handle, ctypes.byref(desc_dev), _vp(dE[j].data_ptr()), _vp(dV.data_ptr()), _vp(dw.data_ptr()),
-                  _vp(d_out["conf"].data_ptr()), _vp(d_out["cw"].data_ptr()), _vp(d_out["agree"].data_ptr()),
-                  _vp(d_out["winner"].data_ptr()), _vp(d_out["rank"].data_ptr()), _vp(stream.cuda_stream))
-                 for j in range(n_rot)]
+    # The timed region is ONE call of lwc_score_batches with a list of K batches (the three resident batches in
+    # rotation): the launches are enqueued by a C loop under one lock, so the overlap of consecutive launches
+    # does not depend on how fast this interpreter comes round (round 1: 0.87 scaling efficiency at 8 GPUs with
+    # K = 20, because eight Python loops contended for the launch path).
+    def batch_list(k):
+        return ctx.batch_list([desc_dev] * k, [dE[j % n_rot].data_ptr() for j in range(k)], [dV.data_ptr()] * k,
+                              [dw.data_ptr()] * k, [d_out["conf"].data_ptr()] * k, [d_out["cw"].data_ptr()] * k,
+                              [d_out["agree"].data_ptr()] * k, [d_out["winner"].data_ptr()] * k,
+                              [d_out["rank"].data_ptr()] * k, stream=stream.cuda_stream)
 
-    def step_device(i):
-        rc = _fn(*_dev_args[i % n_rot])
-        if rc:
-            raise lwc_b200.LwcError(rc, ctx.lib.lwc_last_error_message(ctx.handle).decode())
+    run_warm, run_timed, run_one = batch_list(args.warmup), batch_list(args.steps), batch_list(1)
 
     def step_host():
         ctx.score_raw(desc_host, hE.ptr, hV.ptr, hw.ptr, out_host["conf"].ptr, out_host["cw"].ptr,
@@ -290,16 +388,14 @@ def run_b200(args):
     sampler.start()
 
     # ---- device-resident: W warm-up steps, then exactly K timed steps
-    for i in range(args.warmup):
-        step_device(i)
+    run_warm()
     barrier()
     launches0 = ctx.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.active = True
     with torch.cuda.stream(stream):
         ev0.record(stream)
-        for i in range(args.steps):
-            step_device(i)
+        run_timed()
         ev1.record(stream)
     barrier()
     sampler.active = False
@@ -313,6 +409,9 @@ def run_b200(args):
         per_rank_ms = [float(x.item()) for x in tt]
     ms_per_step = dev_ms / args.steps
     value = world * R * args.steps / (dev_ms * 1e-3)
+    spread = (max(per_rank_ms) - min(per_rank_ms)) / min(per_rank_ms)
+    if spread > 0.03 and rank == 0:
+        print(f"[bench] WARNING: per-rank step times differ by {100 * spread:.1f} % (> 3 %): {per_rank_ms}", file=sys.stderr, flush=True)
 
     # ---- end to end: host buffers in, host buffers out, copies inside the timed region
     e2e_steps = max(3, min(args.steps, 20))
@@ -341,37 +440,59 @@ def run_b200(args):
     sampler.join(timeout=2)
 
     # the two paths must agree bit for bit on the same batch (device batch 0 == host batch)
-    step_device(0)
+    run_one()
     torch.cuda.synchronize()
-    same = bool(np.array_equal(d_out["winner"].cpu().numpy(), out_host["winner"].array))
+    dev_np = {k: v.cpu().numpy() for k, v in d_out.items()}
+    same = all(bool(np.array_equal(dev_np[k], out_host[k].array, equal_nan=True)) for k in dev_np)
+
+    # plain pinned H2D rate of this box: what "PCIe-bound" is measured against (all ranks copy at once, as in the e2e leg)
+    barrier()
+    pcie = h2d_peak(torch, hE.nbytes)
+    barrier()
 
     peak, peak_src = load_peaks()
     bytes_per_launch = R * synth.algorithmic_bytes_per_request(N, D, M)
     achieved = bytes_per_launch / (ms_per_step * 1e-3) / 1e9
+    e2e_gbs = (h2d + d2h) / (e2e_ms / e2e_steps * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{WORKLOAD}: {R} requests x {N} candidates x {D}-dim fp32, {M} voters, per GPU",
+        "config": {"workload": workload_string(R, N, D, M),
                    "similarity": "cosine", "precision": "fp32-grade (3xTF32 compensated Gram)",
                    "kernel": kernel, "parallelism": f"request-sharded x{world}, no collectives",
                    "l2": f"{n_rot} rotating input batches of {hE.nbytes / 1e6:.0f} MB each (> 126 MB L2)",
-                   "launches": "serialised" if args.no_overlap else
-                               "programmatic dependent launch: a launch streams its (resident) inputs while the previous one drains"},
-        "clocks": sampler.summary(), "per_rank_ms_per_step": per_rank_ms,
+                   "launches": ("serialised" if args.no_overlap else
+                                "programmatic dependent launch: a launch streams its (resident) inputs while the previous one drains")
+                               + "; the K timed launches are one lwc_score_batches call"},
+        "clocks": sampler.summary(), "per_rank_ms_per_step": per_rank_ms, "per_rank_spread": spread,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "wall_ms_per_step": wall_ms / e2e_steps,
-                "api": "lwc_score_batch(LWC_MEM_HOST), pinned host buffers"},
+                "api": "lwc_score_batch(LWC_MEM_HOST), pinned host buffers",
+                "achieved_gbs": e2e_gbs, "h2d_peak_gbs": pcie, "frac_of_h2d_peak": e2e_gbs / pcie,
+                "bound": "PCIe: plain pinned cudaMemcpyAsync H2D of the same bytes on this box = h2d_peak_gbs"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": load_traffic(kernel, R), "kernel": kernel, "peak_source": peak_src,
                      "bytes_per_launch": bytes_per_launch, "frac_of_nominal_8000": achieved / 8000.0},
         "host_device_paths_agree": same,
     }
+    if rank == 0:
+        import oracle  # checker only: after every timed region
+
+        sl = slice(0, 256)
+        line["parity_sample"] = parity_sample(oracle, hE.array[sl], V[sl], w[sl], {k: v[sl] for k, v in dev_np.items()})
+    if world == 1:
+        line["gpu_cfg1"] = cfg1_gpu(ctx, lwc_b200, synth)
+    if not args.no_extras:
+        line["extra"] = run_extras(args, torch, lwc_b200, synth, ctx, dist, rank, world, local_rank)
     if world == 1 and not args.no_cpu_baseline:
         if all_cpus:
             os.sched_setaffinity(0, all_cpus)  # the CPU arm owns the whole box again
         line["cpu_baseline"] = cpu_baseline(hE.array, V, w)
+        line["cpu_baseline_cfg1"] = cfg1_cpu()
+        if not args.no_host_leg:
+            line["e2e_from_reference_types"] = host_types_leg(local_rank)
     if rank == 0:
         print(json.dumps(line), flush=True)
     for b in (hE, hV, hw, *out_host.values()):
@@ -380,6 +501,225 @@ def run_b200(args):
     if dist is not None:
         dist.destroy_process_group()
     return 0
+
+
+def host_types_leg(device):
+    """End to end FROM THE REFERENCE'S OWN TYPES: tools/e2e_host (C++) builds cfg2 as per-request
+    CreateEmbeddingResponse-shaped rows of Vec<f64> plus Option<Vec<f64>> votes, submits them to lwc::Batcher from
+    several host threads and collects Tally futures; wall clock.  Returns the tool's JSON (or why it did not run)."""
+    import subprocess
+
+    exe = os.path.join(ROOT, "tools", "e2e_host")
+    if not os.path.exists(exe):
+        return {"unavailable": "tools/e2e_host is not built (python __graft_entry__.py)"}
+    try:
+        out = subprocess.run([exe, "--device", str(device)], capture_output=True, text=True, timeout=300)
+        lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+        if out.returncode != 0 or not lines:
+            return {"unavailable": f"tools/e2e_host exited {out.returncode}: {out.stderr[-300:]}"}
+        return json.loads(lines[-1])
+    except Exception as exc:  # a side leg must never cost the bench line
+        return {"unavailable": repr(exc)}
+
+
+def device_batch(torch, R, N, D, seed):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    e = torch.randn((R, N, D), dtype=torch.float32, device="cuda", generator=g)
+    e *= torch.exp(0.5 * torch.randn((R, N, 1), dtype=torch.float32, device="cuda", generator=g))
+    return e
+
+
+def timed_side_shape(torch, lwc_b200, synth, ctx, dist, R, N, D, M, prec, steps, warmup, seed=7, n_rot=1):
+    """K device-resident launches of one shape (inputs generated in HBM), max over ranks; plus a 256-request
+    parity sample of the outputs.  Returns (ms_per_step, kernel name, parity dict or None)."""
+    from lwc_b200 import shard
+
+    kernel = ctx.kernel_for(R, N, D, M, precision=prec)
+    dE = [device_batch(torch, R, N, D, seed + i) for i in range(n_rot)]
+    V = synth.votes(R, N, M, seed=11)
+    w = synth.weights(R, M, seed=11)
+    dV, dw = torch.from_numpy(V).cuda(), torch.from_numpy(w).cuda()
+    outs = [torch.empty((R, N), dtype=torch.float32, device="cuda"), torch.empty((R, N), dtype=torch.float32, device="cuda"),
+            torch.empty((R, M), dtype=torch.float32, device="cuda"), torch.empty((R,), dtype=torch.int32, device="cuda"),
+            torch.empty((R, N), dtype=torch.int32, device="cuda")]
+    desc = lwc_b200.BatchDesc(R, N, D, M, lwc_b200.SIM_COSINE, prec, lwc_b200.MEM_DEVICE, 1)
+    stream = torch.cuda.Stream()
+
+    def lst(k):
+        return ctx.batch_list([desc] * k, [dE[j % n_rot].data_ptr() for j in range(k)], [dV.data_ptr()] * k, [dw.data_ptr()] * k,
+                              *[[o.data_ptr()] * k for o in outs], stream=stream.cuda_stream)
+
+    lst(warmup)()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    run = lst(steps)
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+        run()
+        ev1.record(stream)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms = shard.max_over_ranks(dist, ev0.elapsed_time(ev1) / steps, device="cuda")
+    par = None
+    if dist is None or dist.get_rank() == 0:
+        import oracle  # checker only
+
+        j = (steps - 1) % n_rot  # the batch the last launch scored
+        n = min(R, 256)
+        got = {"conf": outs[0][:n].cpu().numpy(), "winner": outs[3][:n].cpu().numpy()}
+        tf32 = prec == lwc_b200.PREC_TF32
+        par = parity_sample(oracle, dE[j][:n].cpu().numpy(), V[:n], w[:n], got, rtol=2e-3 if tf32 else 1e-5,
+                            atol=1e-5 if tf32 else 1e-7)
+    del dE, outs
+    torch.cuda.empty_cache()
+    return ms, kernel, par
+
+
+def run_extras(args, torch, lwc_b200, synth, ctx, dist, rank, world, local_rank):
+    """The other BASELINE.json configs, in the record the driver writes: cfg3 strong-scaled by request over the
+    ranks, cfg5's pool shape with rows sharded over the ranks (both exchange routes), cfg4 at N = 1."""
+    from lwc_b200 import shard
+
+    peak, _ = load_peaks()
+    extra = {}
+    steps, warmup = max(3, min(args.steps, 10)), 3
+
+    # ---- cfg3: 65,536 x 32 x 3072, fp32-grade, requests sharded over the ranks (no collective)
+    R_total, N, D, M = synth.CONFIGS["cfg3"]
+    b, e = shard.request_block(R_total, rank, world)
+    ms, kernel, par = timed_side_shape(torch, lwc_b200, synth, ctx, dist, e - b, N, D, M, lwc_b200.PREC_FP32, steps, warmup)
+    gbs = (e - b) * synth.algorithmic_bytes_per_request(N, D, M) / (ms * 1e-3) / 1e9
+    extra["cfg3_strong"] = {"ms": ms, "value": R_total / (ms * 1e-3), "unit": UNIT, "requests_total": R_total,
+                            "requests_per_gpu": e - b, "kernel": kernel, "achieved_gbs_per_gpu": gbs, "frac": gbs / peak,
+                            "efficiency_input": "value at n_gpus / (n_gpus x value at 1)", "steps": steps,
+                            "l2": f"one batch of {(e - b) * N * D * 4 / 1e9:.2f} GB per GPU (> 126 MB L2)", "parity_sample": par}
+
+    # ---- cfg4 (1 GPU only): 8,192 x 128 x 3072, 16 voters, tcgen05, both precisions
+    if world == 1:
+        R4, N4, D4, M4 = synth.CONFIGS["cfg4"]
+        for name, prec in (("cfg4_fp32", lwc_b200.PREC_FP32), ("cfg4_tf32", lwc_b200.PREC_TF32)):
+            ms, kernel, par = timed_side_shape(torch, lwc_b200, synth, ctx, None, R4, N4, D4, M4, prec, steps, warmup)
+            gbs = R4 * synth.algorithmic_bytes_per_request(N4, D4, M4) / (ms * 1e-3) / 1e9
+            extra[name] = {"ms": ms, "value": R4 / (ms * 1e-3), "unit": UNIT, "kernel": kernel, "achieved_gbs": gbs,
+                           "frac": gbs / peak, "algorithmic_tflops": R4 * synth.algorithmic_flops_per_request(N4, D4, M4) / (ms * 1e-3) / 1e12,
+                           "steps": steps, "parity_sample": par}
+
+    # ---- cfg5's shape: one pool of 32,768 x world rows x 1024, 16 voters, rows sharded over the ranks
+    try:
+        extra["cfg5_pool"] = pool_extra(torch, lwc_b200, dist, rank, world, local_rank, steps=5, warmup=2)
+    except Exception as exc:  # never lose the bench line to a side leg
+        extra["cfg5_pool"] = {"failed": repr(exc)}
+    return extra
+
+
+def pool_extra(torch, lwc_b200, dist, rank, world, local_rank, steps, warmup, n_own=32768, D=1024, M=16):
+    import ctypes
+
+    from lwc_b200 import shard
+
+    n_total = n_own * world
+    ctx = lwc_b200.Context(device=local_rank)
+    if world > 1:
+        ident = lwc_b200.comm_unique_id() if rank == 0 else bytes(128)
+        ident = shard.broadcast_bytes(dist, ident, src=0, device="cuda")
+        ctx.comm_init(world, rank, ident)
+    # host-generated rows (so that rank 0 can check the whole pool against the CPU oracle's O(N D) identity)
+    rng = np.random.default_rng(100 + rank)
+    cent = np.random.default_rng(99).standard_normal((8, D)).astype(np.float32)
+    E_h = cent[rng.integers(0, 8, n_own)] * 0.5 + rng.standard_normal((n_own, D), dtype=np.float32)
+    V_h = rng.random((M, n_own), dtype=np.float32) ** 6
+    V_h /= V_h.sum(axis=1, keepdims=True) * np.float32(world)  # a voter's whole row (all ranks) sums to 1
+    w_h = np.linspace(0.5, 2.0, M).astype(np.float32)
+    E, V, w = torch.from_numpy(E_h).cuda(), torch.from_numpy(V_h).cuda(), torch.from_numpy(w_h).cuda()
+    conf = torch.empty((n_own,), dtype=torch.float32, device="cuda")
+    cw = torch.empty((n_own,), dtype=torch.float32, device="cuda")
+    agree = torch.empty((M,), dtype=torch.float32, device="cuda")
+    winner = torch.zeros((1,), dtype=torch.int64, device="cuda")
+    desc = lwc_b200.PoolDesc(n_own, D, M, lwc_b200.PREC_BF16, lwc_b200.MEM_DEVICE)
+    vp = ctypes.c_void_p
+
+    def step():
+        rc = ctx.lib.lwc_pool_consensus(ctx.handle, ctypes.byref(desc), vp(E.data_ptr()), vp(V.data_ptr()), vp(w.data_ptr()),
+                                        vp(conf.data_ptr()), vp(cw.data_ptr()), vp(agree.data_ptr()), vp(winner.data_ptr()), None)
+        if rc:
+            raise lwc_b200.LwcError(rc, ctx.lib.lwc_last_error_message(ctx.handle).decode())
+
+    def timed():
+        for _ in range(warmup):
+            step()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ext = torch.cuda.ExternalStream(ctx.stream())
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(ext)
+        for _ in range(steps):
+            step()  # blocking: returns when the call's stream has drained
+        e1.record(ext)
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        return shard.max_over_ranks(dist, e0.elapsed_time(e1) / steps, device="cuda")
+
+    def gather_result():
+        """(whole-pool confidences on rank 0, winners of all ranks, sum of confidences)"""
+        if dist is None:
+            return conf.cpu().numpy(), [int(winner.item())], float(conf.sum().item())
+        parts = [torch.empty_like(conf) for _ in range(world)]
+        dist.all_gather(parts, conf)
+        wins = [torch.zeros_like(winner) for _ in range(world)]
+        dist.all_gather(wins, winner)
+        allc = torch.cat(parts)
+        return allc.cpu().numpy(), [int(x.item()) for x in wins], float(allc.double().sum().item())
+
+    try:
+        bf16_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+    except Exception:
+        bf16_peak = 1590.0
+    flops_per_gpu = 2.0 * n_total * n_total * D / world
+    routes = [("nccl_allgather" if world > 1 else "single_gpu", False)] + ([("fused_p2p_gather", True)] if world > 1 else [])
+    want = None
+    if world > 1:  # rank 0 needs the whole pool for the check
+        Es = [torch.empty_like(E) for _ in range(world)]
+        Vs = [torch.empty_like(V) for _ in range(world)]
+        dist.all_gather(Es, E)
+        dist.all_gather(Vs, V)
+        if rank == 0:
+            E_all = torch.cat(Es).cpu().numpy()
+            V_all = torch.cat(Vs, dim=1).cpu().numpy()
+        del Es, Vs
+    else:
+        E_all, V_all = E_h, V_h
+    if rank == 0:
+        import oracle  # checker only
+
+        want = oracle.pool_f64(E_all, V_all, w_h, method=1)  # O(N D) centroid identity (SURVEY 8.0 note)
+    out = {"rows_total": n_total, "rows_per_gpu": n_own, "D": D, "voters": M, "routes": []}
+    for name, fused in routes:
+        if fused:
+            mine = ctx.pool_p2p_export(n_own, D)
+            buf = torch.frombuffer(bytearray(mine), dtype=torch.uint8).cuda()
+            bufs = [torch.empty_like(buf) for _ in range(world)]
+            dist.all_gather(bufs, buf)
+            ctx.pool_p2p_attach(b"".join(bytes(x.cpu().numpy().tobytes()) for x in bufs))
+        ms = timed()
+        allc, wins, total = gather_result()
+        rec = {"route": name, "ms": ms, "tflops_per_gpu": flops_per_gpu / (ms * 1e-3) / 1e12,
+               "frac_of_bf16_peak": flops_per_gpu / (ms * 1e-3) / 1e12 / bf16_peak, "winner_same": len(set(wins)) == 1,
+               "sum_conf": total, "steps": steps}
+        if rank == 0:
+            top = float(want["conf"].max())
+            rec["max_conf_err_over_top"] = float(np.max(np.abs(allc - want["conf"])) / top)
+            rec["winner_is_oracles"] = bool(wins[0] == want["winner"])
+            rec["check_passed"] = bool(rec["max_conf_err_over_top"] <= 1e-2 and rec["winner_same"] and abs(total - 1.0) < 1e-3)
+        out["routes"].append(rec)
+    if world > 1:
+        ctx.comm_destroy()
+    ctx.close()
+    return out
 
 
 def run_other_workload(args, torch, lwc_b200, synth, local_rank, rank=0, world=1, dist=None):
@@ -401,42 +741,8 @@ def run_other_workload(args, torch, lwc_b200, synth, local_rank, rank=0, world=1
     R = e - b
     prec = {"fp32": lwc_b200.PREC_FP32, "tf32": lwc_b200.PREC_TF32}[args.precision]
     ctx = lwc_b200.Context(device=local_rank)
-    kernel = ctx.kernel_for(R, N, D, M, precision=prec)
-    g = torch.Generator(device="cuda").manual_seed(7)
     n_rot = 2
-    dE = []
-    for _ in range(n_rot):
-        e = torch.randn((R, N, D), dtype=torch.float32, device="cuda", generator=g)
-        e *= torch.exp(0.5 * torch.randn((R, N, 1), dtype=torch.float32, device="cuda", generator=g))
-        dE.append(e)
-    V = synth.votes(R, N, M, seed=11)
-    w = synth.weights(R, M, seed=11)
-    dV, dw = torch.from_numpy(V).cuda(), torch.from_numpy(w).cuda()
-    outs = [torch.empty((R, N), dtype=torch.float32, device="cuda"), torch.empty((R, N), dtype=torch.float32, device="cuda"),
-            torch.empty((R, M), dtype=torch.float32, device="cuda"), torch.empty((R,), dtype=torch.int32, device="cuda"),
-            torch.empty((R, N), dtype=torch.int32, device="cuda")]
-    desc = lwc_b200.BatchDesc(R, N, D, M, lwc_b200.SIM_COSINE, prec, lwc_b200.MEM_DEVICE, 1)
-    stream = torch.cuda.Stream()
-
-    def step(i):
-        ctx.score_raw(desc, dE[i % n_rot].data_ptr(), dV.data_ptr(), dw.data_ptr(), *[o.data_ptr() for o in outs],
-                      stream=stream.cuda_stream)
-
-    for i in range(args.warmup):
-        step(i)
-    if dist is not None:
-        dist.barrier()
-    torch.cuda.synchronize()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with torch.cuda.stream(stream):
-        ev0.record(stream)
-        for i in range(args.steps):
-            step(i)
-        ev1.record(stream)
-    torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
-    ms = shard.max_over_ranks(dist, ev0.elapsed_time(ev1) / args.steps, device="cuda")
+    ms, kernel, par = timed_side_shape(torch, lwc_b200, synth, ctx, dist, R, N, D, M, prec, args.steps, args.warmup, n_rot=n_rot)
     peak, peak_src = load_peaks()
     nbytes = R * synth.algorithmic_bytes_per_request(N, D, M)  # per GPU: the roofline is a per-GPU statement
     flops = R * synth.algorithmic_flops_per_request(N, D, M)
@@ -452,10 +758,11 @@ def run_other_workload(args, torch, lwc_b200, synth, local_rank, rank=0, world=1
             "config": {"workload": f"{args.workload}: {R_total} requests x {N} candidates x {D}-dim fp32, {M} voters"
                                    + (f", sharded by request x{world} ({R} per GPU), no collective" if world > 1 else ""),
                        "kernel": kernel, "precision": args.precision,
-                       "l2": f"{n_rot} rotating batches of {dE[0].numel() * 4 / 1e9:.2f} GB per GPU"},
+                       "l2": f"{n_rot} rotating batches of {R * N * D * 4 / 1e9:.2f} GB per GPU"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "peak_source": peak_src, "bytes_per_launch": nbytes, "scope": "per GPU",
                          "algorithmic_tflops": flops / (ms * 1e-3) / 1e12},
+            "parity_sample": par,
             "gpu_launches": args.steps}), flush=True)
     ctx.close()
     if dist is not None:
@@ -655,6 +962,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e", action="store_true", help="side workloads cfg3/cfg4: add the host-buffer path and the CPU port")
+    ap.add_argument("--no-extras", action="store_true", help="skip the cfg3 / cfg4 / cfg5 side records of the main line")
+    ap.add_argument("--no-host-leg", action="store_true", help="skip tools/e2e_host (end to end from the reference's types)")
     ap.add_argument("--no-overlap", action="store_true", help="do not set LWC_CTX_INPUTS_RESIDENT (launches fully serialised)")
     ap.add_argument("--workload", default=WORKLOAD, choices=["cfg2", "cfg3", "cfg4", "cfg2x4", "pool", "table", "vote"],
                     help="cfg2 is the bench line; cfg3/cfg4 are kernel-only side measurements")

@@ -18,9 +18,12 @@
  *                            nothing else.
  *   lwc_merge_error_codes .. the all-votes-failed status merge, client.rs:386-409,459-463
  *                            and src/score/completions/error.rs:41.
- *   lwc_stage_f64 .......... the Vec<f64> -> device fp32 hop for
+ *   lwc_stage_f64,
+ *   lwc_stage_f64_bf16,
+ *   lwc_score_batch_typed .. the Vec<f64> -> device fp32 hop for
  *                            embeddings::response::Embedding.embedding
- *                            (src/embeddings/response.rs:19-24).
+ *                            (src/embeddings/response.rs:19-24): on the host (fp32 or bf16
+ *                            transport) or on the device (f64 transport).
  *   lwc_pool_consensus ..... client.rs:384-456 for ONE request whose pool is too large for a
  *                            batch slot (BASELINE.json config 5: 262,144 candidates), rows
  *                            sharded over the GPUs of a node; no other reference counterpart.
@@ -32,8 +35,9 @@
  *                            the reference ships as unimplemented!(), src/score/completions/weight.rs:99-117
  *                            (config src/score/model/mod.rs:278-306, limits src/score/llm/mod.rs:663-688);
  *                            build-defined policy, no reference arithmetic to match.
- *   lwc_pool_consensus_static, lwc_comm_*, lwc_pool_p2p_*, lwc_host_* / lwc_device_* / lwc_memcpy,
- *   lwc_ctx_* .............. no reference counterpart (allocation-free variant, multi-GPU plumbing, lifecycle).
+ *   lwc_score_batches, lwc_pool_consensus_static, lwc_comm_*, lwc_pool_p2p_*, lwc_host_* / lwc_device_* /
+ *   lwc_memcpy, lwc_ctx_* .. no reference counterpart (batch lists, allocation-free variant, multi-GPU
+ *                            plumbing, lifecycle).
  *
  * Error convention mirrors error::ResponseError { code: u16, .. } (src/error.rs:8-13):
  * every function returns 0 on success or an HTTP-style status -- 400 for a malformed
@@ -149,6 +153,42 @@ int32_t lwc_stream_synchronize(lwc_ctx *ctx, void *stream);
 int32_t lwc_score_batch(lwc_ctx *ctx, const lwc_batch_desc *desc, const float *E, const float *V,
                         const float *w, float *conf, float *cw, float *agree, int32_t *winner,
                         int32_t *rank, void *stream);
+
+/* replaces: the element-type hop of Embedding.embedding (Vec<f64>, src/embeddings/response.rs:21; JSON floats on
+ * the wire) on the way to the kernels.  lwc_score_batch for embeddings that are not fp32 when they reach the
+ * library: E is [R][N][D] of `e_type`, 16-byte aligned, host or device memory per desc->memory; everything else as
+ * in lwc_score_batch.
+ *   LWC_ELEM_F64   the reference's own element type.  8 bytes per element cross PCIe and a streaming kernel rounds
+ *                  them to fp32 (nearest even) on the device: the results are the bits of converting on the host
+ *                  (lwc_stage_f64) and calling lwc_score_batch.  For hosts whose f64 rows already sit in pinned
+ *                  memory; a host that has to touch every row anyway should convert while it copies (fp32 halves
+ *                  the PCIe time, which is what bounds a host-memory call: DESIGN.md 3.9).
+ *   LWC_ELEM_BF16  OPT-IN reduced transport: 2 bytes per element cross PCIe (lwc_stage_f64_bf16 converts on the
+ *                  host), expanded exactly on the device and scored with fp32 accumulate -- the tensor core
+ *                  reads a bf16 value exactly, so one pass suffices whatever desc->precision says.  The inputs
+ *                  carry 8 mantissa bits: stated tolerance 1e-2 of a request's top confidence, winner exact
+ *                  where the oracle's margin exceeds that.
+ * Device-memory calls convert into one buffer owned by the context: issue them on one stream. */
+enum { LWC_ELEM_F32 = 0, LWC_ELEM_F64 = 1, LWC_ELEM_BF16 = 2 };
+int32_t lwc_score_batch_typed(lwc_ctx *ctx, const lwc_batch_desc *desc, int32_t e_type, const void *E, const float *V,
+                              const float *w, float *conf, float *cw, float *agree, int32_t *winner, int32_t *rank,
+                              void *stream);
+/* Host helper for LWC_ELEM_BF16: n doubles -> n bf16 (round to nearest even).  Like lwc_stage_f64 it is a plain
+ * loop meant to be called by many threads on their own rows. */
+int32_t lwc_stage_f64_bf16(lwc_ctx *ctx, const double *src, size_t n, uint16_t *dst);
+
+/* No counterpart in the reference (which scores one request per task): lwc_score_batch for a LIST of
+ * device-resident batches, enqueued back to back on `stream` inside one call.  descs [n_batches]; every
+ * other argument is an array of n_batches pointers with lwc_score_batch's meaning (an output array, or an
+ * entry of one, may be NULL).  Every batch must be LWC_MEM_DEVICE.  The list is validated before the first
+ * launch: a 400 means nothing was enqueued.  Results are bit-identical to n_batches single calls; what
+ * changes is the host side -- one lock, one argument check and one library call per list instead of per
+ * batch -- so a producer that already holds several batches in HBM keeps the GPU's launch queue full
+ * (with LWC_CTX_INPUTS_RESIDENT consecutive launches overlap only while the host stays a launch ahead of
+ * a ~60 us kernel).  Asynchronous on `stream` like a device-memory lwc_score_batch. */
+int32_t lwc_score_batches(lwc_ctx *ctx, int32_t n_batches, const lwc_batch_desc *descs, const float *const *E,
+                          const float *const *V, const float *const *w, float *const *conf, float *const *cw,
+                          float *const *agree, int32_t *const *winner, int32_t *const *rank, void *stream);
 
 /* Name of the kernel lwc_score_batch would launch for this descriptor ("small16_tf32x3", ...);
  * empty string for an invalid descriptor.  For logs, tests and the bench's roofline record. */

@@ -15,6 +15,8 @@
 #include "score_small.cuh"
 #include "score_stream.cuh"
 #include "score_tc.cuh"
+#include "score_tc16.cuh"
+#include "convert.cuh"
 #include "vote_kernel.cuh"
 
 #define LWC_VERSION_STRING "lwc_b200 0.1.0 (sm_100a)"
@@ -105,7 +107,7 @@ Plan plan_for(const lwc_batch_desc &d, const void *E) {
         pl.route = ROUTE_TC;
         pl.np = 128;
         pl.x3 = (d.precision == LWC_PREC_FP32 || d.precision == LWC_PREC_TF32X3);
-        pl.name = pl.x3 ? "tc128_tf32x3" : "tc128_tf32";
+        pl.name = pl.x3 ? "tc128_f16x2" : "tc128_tf32"; // LWC_TC_X3=tf32 runs the fp32-grade route on tf32 pieces ("tc128_tf32x3")
         return pl;
     }
     pl.route = ROUTE_GENERIC;
@@ -130,34 +132,47 @@ cudaError_t launch_generic(const lwc::ScoreParams &p, cudaStream_t st) {
     return cudaGetLastError();
 }
 
-template <int NT, bool X3, int KW, int U>
+template <int NT, bool X3, int KW, int U, bool F16>
 cudaError_t launch_small_one(const lwc::ScoreParams &p, cudaStream_t st) {
     using C = lwc::SmallCfg<NT, X3, KW, U>;
     static std::atomic<bool> configured[64]; // zero-initialised; set once per device (contexts on other threads may race here)
     int dev = 0;
     cudaGetDevice(&dev);
     if (!configured[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(lwc::score_small_kernel<NT, X3, KW, U>,
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_small_kernel<NT, X3, KW, U, F16>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem_bytes());
         if (e != cudaSuccess) return e;
         configured[dev & 63] = true;
     }
-    lwc::score_small_kernel<NT, X3, KW, U><<<p.R, KW * 32, C::smem_bytes(), st>>>(p);
+    lwc::score_small_kernel<NT, X3, KW, U, F16><<<p.R, KW * 32, C::smem_bytes(), st>>>(p);
     return cudaGetLastError();
 }
 
+// f16: fp32-grade route on fp16 pieces (default for X3; LWC_SMALL_X3=tf32 keeps tf32 pieces)
 template <int NT, bool X3>
-cudaError_t launch_small(const lwc::ScoreParams &p, cudaStream_t st, int kw, int u) {
+cudaError_t launch_small(const lwc::ScoreParams &p, cudaStream_t st, int kw, int u, bool f16) {
     if (u == 0) u = (NT == 16) ? 4 : 2;
+    constexpr bool F = X3; // the fp16-piece instantiations exist for the fp32-grade route only
     const int key = kw * 10 + u;
+    if (F && f16) {
+        switch (key) {
+            case 22: return launch_small_one<NT, X3, 2, 2, F>(p, st);
+            case 24: return launch_small_one<NT, X3, 2, 4, F>(p, st);
+            case 42: return launch_small_one<NT, X3, 4, 2, F>(p, st);
+            case 44: return launch_small_one<NT, X3, 4, 4, F>(p, st);
+            case 82: return launch_small_one<NT, X3, 8, 2, F>(p, st);
+            case 84: return launch_small_one<NT, X3, 8, 4, F>(p, st);
+            default: return launch_small_one<NT, X3, 4, 2, F>(p, st);
+        }
+    }
     switch (key) {
-        case 22: return launch_small_one<NT, X3, 2, 2>(p, st);
-        case 24: return launch_small_one<NT, X3, 2, 4>(p, st);
-        case 42: return launch_small_one<NT, X3, 4, 2>(p, st);
-        case 44: return launch_small_one<NT, X3, 4, 4>(p, st);
-        case 82: return launch_small_one<NT, X3, 8, 2>(p, st);
-        case 84: return launch_small_one<NT, X3, 8, 4>(p, st);
-        default: return launch_small_one<NT, X3, 4, 2>(p, st);
+        case 22: return launch_small_one<NT, X3, 2, 2, false>(p, st);
+        case 24: return launch_small_one<NT, X3, 2, 4, false>(p, st);
+        case 42: return launch_small_one<NT, X3, 4, 2, false>(p, st);
+        case 44: return launch_small_one<NT, X3, 4, 4, false>(p, st);
+        case 82: return launch_small_one<NT, X3, 8, 2, false>(p, st);
+        case 84: return launch_small_one<NT, X3, 8, 4, false>(p, st);
+        default: return launch_small_one<NT, X3, 4, 2, false>(p, st);
     }
 }
 
@@ -176,7 +191,7 @@ bool make_tensor_map_tc(CUtensorMap *tm, const float *E, int R, int N, int D, in
 }
 
 template <bool X3>
-cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
+cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st, const int *fix_flags = nullptr) {
     lwc::TcGeom geo;
     geo.ko = ctx->tc_ko > 0 ? ctx->tc_ko : (X3 ? 2 : 4); // 64 KB per stage either way (profiles/r1_tma_probe2.txt)
     const int nslab = p.D / 32;
@@ -197,8 +212,44 @@ cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) 
     if (!make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, X3 ? 1 : geo.ko)) return cudaErrorInvalidValue;
     const int grid = p.R < ctx->sm_count ? p.R : ctx->sm_count;
     lwc::score_tc_kernel<X3><<<grid, X3 ? lwc::kTcThreadsX3 : lwc::kTcThreads, lwc::tc_smem_bytes(geo.ko, geo.stages, X3), st>>>(
-        tm, p, geo);
+        tm, p, geo, fix_flags);
     return cudaGetLastError();
+}
+
+// fp32-grade route at kind::f16 rate (score_tc16.cuh) + its fix-up pass: the requests whose norms fall outside
+// what fp16 pieces represent exactly enough are marked by the first kernel and re-scored by the tf32 kernel.
+cudaError_t launch_tc16(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
+    lwc::TcGeom geo;
+    geo.ko = 2;
+    geo.stages = lwc::kT16MaxStages;
+    while (geo.stages > 2 && lwc::tc16_smem_bytes(geo.stages) > (size_t)ctx->max_smem_optin) --geo.stages;
+    if (ctx->tc_stages > 1 && ctx->tc_stages < geo.stages) geo.stages = ctx->tc_stages;
+    if (lwc::tc16_smem_bytes(geo.stages) > (size_t)ctx->max_smem_optin) return cudaErrorInvalidConfiguration;
+    static std::atomic<bool> configured[64];
+    if (!configured[ctx->device & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_tc16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
+        if (e != cudaSuccess) return e;
+        configured[ctx->device & 63] = true;
+    }
+    if ((size_t)p.R * sizeof(int) > ctx->tc_flags_cap) { // one word per request: which requests need the fix-up pass
+        if (ctx->tc_flags) {
+            cudaError_t e = cudaFree(ctx->tc_flags);
+            if (e != cudaSuccess) return e;
+        }
+        ctx->tc_flags = nullptr, ctx->tc_flags_cap = 0;
+        const size_t want = (size_t)p.R * sizeof(int) * 2 + 256;
+        cudaError_t e = cudaMalloc(&ctx->tc_flags, want);
+        if (e != cudaSuccess) return e;
+        ctx->tc_flags_cap = want;
+    }
+    CUtensorMap tm;
+    if (!make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, 2)) return cudaErrorInvalidValue;
+    const int grid = p.R < ctx->sm_count ? p.R : ctx->sm_count;
+    lwc::score_tc16_kernel<<<grid, lwc::kT16Threads, lwc::tc16_smem_bytes(geo.stages), st>>>(tm, p, geo, static_cast<int *>(ctx->tc_flags));
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    ctx->launches++;
+    return launch_tc<true>(ctx, p, st, static_cast<const int *>(ctx->tc_flags));
 }
 
 template <int NT, bool X3, int NCW, int NF>
@@ -264,7 +315,7 @@ int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStr
     // HBM; there the one-CTA-per-request kernel (more warps in flight) measured 83 % vs 80 % of HBM peak.
     const bool stream_route = ctx->small_impl == 0 && !(pl.np == 32 && pl.x3 && !ctx->force_stream);
     if (pl.route == ROUTE_TC) {
-        e = pl.x3 ? launch_tc<true>(ctx, p, st) : launch_tc<false>(ctx, p, st);
+        e = !pl.x3 ? launch_tc<false>(ctx, p, st) : (ctx->tc_x3_tf32 ? launch_tc<true>(ctx, p, st) : launch_tc16(ctx, p, st));
     } else if (pl.route == ROUTE_SMALL && stream_route) {
         if (pl.np == 16)
             e = pl.x3 ? launch_stream<16, true>(ctx, p, st) : launch_stream<16, false>(ctx, p, st);
@@ -272,11 +323,11 @@ int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStr
             e = pl.x3 ? launch_stream<32, true>(ctx, p, st) : launch_stream<32, false>(ctx, p, st);
     } else if (pl.route == ROUTE_SMALL) {
         if (pl.np == 16)
-            e = pl.x3 ? launch_small<16, true>(p, st, ctx->small_kw, ctx->small_u)
-                      : launch_small<16, false>(p, st, ctx->small_kw, ctx->small_u);
+            e = pl.x3 ? launch_small<16, true>(p, st, ctx->small_kw, ctx->small_u, !ctx->small_x3_tf32)
+                      : launch_small<16, false>(p, st, ctx->small_kw, ctx->small_u, false);
         else // 32-row pools: 2 warps per request measured best (1.157 vs 1.185 ms at KW=4, cfg3 slice)
-            e = pl.x3 ? launch_small<32, true>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u)
-                      : launch_small<32, false>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u);
+            e = pl.x3 ? launch_small<32, true>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u, !ctx->small_x3_tf32)
+                      : launch_small<32, false>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u, false);
     } else {
         if (pl.np == 32)
             e = launch_generic<32>(p, st);
@@ -301,16 +352,36 @@ int ensure(lwc_ctx *ctx, Slot &s, int which, size_t bytes) {
     return LWC_OK;
 }
 
-int score_host(lwc_ctx *ctx, const lwc_batch_desc &d, const Plan &pl, const float *E, const float *V, const float *w,
+size_t elem_size(int e_type) { return e_type == LWC_ELEM_F64 ? 8 : (e_type == LWC_ELEM_BF16 ? 2 : 4); }
+
+// raw (f64 / bf16) -> fp32 on `st`; both device pointers 16-byte aligned (cudaMalloc)
+int launch_convert(lwc_ctx *ctx, int e_type, const void *raw, float *dst, size_t n, cudaStream_t st) {
+    if (n == 0) return LWC_OK;
+    const size_t per_block = 256 * (e_type == LWC_ELEM_F64 ? 4 : 8);
+    size_t blocks = (n + per_block - 1) / per_block;
+    const size_t cap = (size_t)ctx->sm_count * 8; // grid-stride: eight resident CTAs per SM keep the loads in flight
+    if (blocks > cap) blocks = cap;
+    if (e_type == LWC_ELEM_F64)
+        lwc::convert_f64_f32_kernel<<<(unsigned)blocks, 256, 0, st>>>(static_cast<const double *>(raw), dst, n);
+    else
+        lwc::expand_bf16_f32_kernel<<<(unsigned)blocks, 256, 0, st>>>(static_cast<const uint16_t *>(raw), dst, n);
+    CUDA_TRY(ctx, cudaGetLastError());
+    ctx->launches++;
+    return LWC_OK;
+}
+
+int score_host(lwc_ctx *ctx, const lwc_batch_desc &d, const Plan &pl, int e_type, const void *E, const float *V, const float *w,
                float *conf, float *cw, float *agree, int32_t *winner, int32_t *rank) {
     const bool cosine = d.similarity == LWC_SIM_COSINE;
-    const size_t e_req = cosine ? (size_t)d.N * d.D * sizeof(float) : 0;
+    const size_t e_req = cosine ? (size_t)d.N * d.D * sizeof(float) : 0;         // fp32 tile the kernels read
+    const size_t e_raw = cosine ? (size_t)d.N * d.D * elem_size(e_type) : 0;     // what crosses PCIe
+    const bool typed = e_type != LWC_ELEM_F32;
     const size_t v_req = (size_t)d.M * d.N * sizeof(float);
     int chunk = ctx->chunk_requests;
     if (chunk <= 0) {
         // ~96 MiB of embeddings per chunk: PCIe efficiency peaks there (measured: 548 k req/s at 32 MiB,
         // 555 k at 96-192 MiB on cfg2) and four chunks still overlap copies with kernels
-        size_t per = e_req + v_req + 64;
+        size_t per = e_raw + v_req + 64;
         chunk = (int)((96u << 20) / per);
         if (chunk < 1) chunk = 1;
     }
@@ -333,14 +404,15 @@ int score_host(lwc_ctx *ctx, const lwc_batch_desc &d, const Plan &pl, const floa
         if (s.used) CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copy_stream, s.all_done, 0));
         // (re)allocation happens only while growing; cudaFree synchronises, which is safe here
         if ((rc = ensure(ctx, s, 0, e_req * rc_n))) return rc;
+        if (typed && (rc = ensure(ctx, s, 6, e_raw * rc_n))) return rc; // f64 / bf16 as it arrived
         if ((rc = ensure(ctx, s, 1, v_req * rc_n))) return rc;
         if ((rc = ensure(ctx, s, 2, (size_t)d.M * rc_n * sizeof(float)))) return rc;
         if ((rc = ensure(ctx, s, 3, (size_t)d.N * rc_n * sizeof(float) * 2))) return rc;             // conf | cw
         if ((rc = ensure(ctx, s, 4, (size_t)d.M * rc_n * sizeof(float)))) return rc;                 // agree
         if ((rc = ensure(ctx, s, 5, (size_t)rc_n * sizeof(int32_t) * ((size_t)d.N + 1)))) return rc; // winner | rank
         if (cosine)
-            CUDA_TRY(ctx, cudaMemcpyAsync(s.buf[0], E + (size_t)r0 * d.N * d.D, e_req * rc_n, cudaMemcpyHostToDevice,
-                                          ctx->copy_stream));
+            CUDA_TRY(ctx, cudaMemcpyAsync(typed ? s.buf[6] : s.buf[0], static_cast<const char *>(E) + (size_t)r0 * e_raw, e_raw * rc_n,
+                                          cudaMemcpyHostToDevice, ctx->copy_stream));
         if (v_req)
             CUDA_TRY(ctx, cudaMemcpyAsync(s.buf[1], V + (size_t)r0 * d.M * d.N, v_req * rc_n, cudaMemcpyHostToDevice,
                                           ctx->copy_stream));
@@ -349,6 +421,9 @@ int score_host(lwc_ctx *ctx, const lwc_batch_desc &d, const Plan &pl, const floa
                                           cudaMemcpyHostToDevice, ctx->copy_stream));
         CUDA_TRY(ctx, cudaEventRecord(s.h2d_done, ctx->copy_stream));
         CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, s.h2d_done, 0));
+        if (typed && cosine &&
+            (rc = launch_convert(ctx, e_type, s.buf[6], static_cast<float *>(s.buf[0]), (size_t)rc_n * d.N * d.D, ctx->stream)))
+            return rc;
 
         lwc::ScoreParams p;
         p.E = static_cast<const float *>(s.buf[0]);
@@ -449,6 +524,8 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     if (const char *s = getenv("LWC_POOL_NO_P2P")) ctx->no_p2p = atoi(s);
     if (const char *s = getenv("LWC_CHUNK_REQUESTS")) ctx->chunk_requests = atoi(s);
     if (const char *s = getenv("LWC_TC_KO")) ctx->tc_ko = atoi(s);
+    if (const char *s = getenv("LWC_TC_X3")) ctx->tc_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
+    if (const char *s = getenv("LWC_SMALL_X3")) ctx->small_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_TC_STAGES")) ctx->tc_stages = atoi(s);
     if (ctx->stream_ncw != 0 && ctx->stream_ncw != 4 && ctx->stream_ncw != 8 && ctx->stream_ncw != 12) ctx->stream_ncw = 0;
     if (ctx->stream_kc < 0 || ctx->stream_kc % 16) ctx->stream_kc = 0;
@@ -479,6 +556,8 @@ void lwc_ctx_destroy(lwc_ctx *ctx) {
         for (auto &q : m)
             if (q) cudaIpcCloseMemHandle(q);
     if (ctx->p2p_dev) cudaFree(ctx->p2p_dev);
+    if (ctx->typed_buf) cudaFree(ctx->typed_buf);
+    if (ctx->tc_flags) cudaFree(ctx->tc_flags);
     for (auto &b : ctx->table_buf)
         if (b) cudaFree(b);
     for (auto &b : ctx->pool_buf)
@@ -550,37 +629,119 @@ const char *lwc_kernel_for(const lwc_ctx *ctx, const lwc_batch_desc *desc) {
     (void)ctx;
     if (!desc) return "";
     // alignment is unknown here: assume the documented 16-byte alignment of E
-    return plan_for(*desc, nullptr).name;
+    const Plan pl = plan_for(*desc, nullptr);
+    if (ctx && ctx->tc_x3_tf32 && pl.route == ROUTE_TC && pl.x3) return "tc128_tf32x3";
+    if (ctx && pl.route == ROUTE_SMALL && pl.x3 && !ctx->small_x3_tf32) {
+        // the one-CTA-per-request kernel runs the fp32-grade Gram on fp16 pieces; the persistent ring kernel on tf32 pieces
+        const bool stream_route = ctx->small_impl == 0 && !(pl.np == 32 && !ctx->force_stream);
+        if (!stream_route) return pl.np == 16 ? "small16_f16x2" : "small32_f16x2";
+    }
+    return pl.name;
 }
 
 uint64_t lwc_launch_count(const lwc_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
-int32_t lwc_score_batch(lwc_ctx *ctx, const lwc_batch_desc *desc, const float *E, const float *V, const float *w,
-                        float *conf, float *cw, float *agree, int32_t *winner, int32_t *rank, void *stream) {
+static int32_t score_typed(lwc_ctx *ctx, const char *fn, const lwc_batch_desc *desc, int e_type, const void *E, const float *V,
+                           const float *w, float *conf, float *cw, float *agree, int32_t *winner, int32_t *rank, void *stream) {
     if (!ctx) return LWC_ERR_INVALID;
     std::lock_guard<std::mutex> lk(ctx->mu);
-    if (!desc) return fail(ctx, LWC_ERR_INVALID, "lwc_score_batch: desc is NULL");
-    const lwc_batch_desc d = *desc;
-    const Plan pl = plan_for(d, E);
+    if (!desc) return fail(ctx, LWC_ERR_INVALID, "%s: desc is NULL", fn);
+    lwc_batch_desc d = *desc;
+    if (e_type != LWC_ELEM_F32 && e_type != LWC_ELEM_F64 && e_type != LWC_ELEM_BF16)
+        return fail(ctx, LWC_ERR_INVALID, "%s: element type %d is not LWC_ELEM_F32 / _F64 / _BF16", fn, e_type);
+    // bf16 inputs are exact in tf32 (8 of its 10 mantissa bits): the error-compensating second product would be zeros
+    if (e_type == LWC_ELEM_BF16 && (d.precision == LWC_PREC_FP32 || d.precision == LWC_PREC_TF32X3 || d.precision == LWC_PREC_BF16))
+        d.precision = LWC_PREC_TF32;
+    const bool typed = e_type != LWC_ELEM_F32;
+    // typed embeddings are converted into a 16-byte aligned fp32 buffer of the library's own: plan for that
+    const Plan pl = plan_for(d, typed ? nullptr : E);
     if (pl.route == ROUTE_INVALID)
         return fail(ctx, LWC_ERR_INVALID,
-                    "lwc_score_batch: invalid descriptor (R=%d N=%d D=%d M=%d sim=%d prec=%d mem=%d); need R>=0, "
+                    "%s: invalid descriptor (R=%d N=%d D=%d M=%d sim=%d prec=%d mem=%d); need R>=0, "
                     "1<=N<=%d, 0<=M<=%d, D>=1 for cosine",
-                    d.R, d.N, d.D, d.M, d.similarity, d.precision, d.memory, LWC_MAX_CHOICES, LWC_MAX_VOTERS);
+                    fn, d.R, d.N, d.D, d.M, d.similarity, d.precision, d.memory, LWC_MAX_CHOICES, LWC_MAX_VOTERS);
     if (d.R == 0) return LWC_OK;
-    if (d.similarity == LWC_SIM_COSINE && !E) return fail(ctx, LWC_ERR_INVALID, "lwc_score_batch: E is NULL");
-    if (d.M > 0 && (!V || !w)) return fail(ctx, LWC_ERR_INVALID, "lwc_score_batch: V or w is NULL with M > 0");
+    const bool cosine = d.similarity == LWC_SIM_COSINE;
+    if (cosine && !E) return fail(ctx, LWC_ERR_INVALID, "%s: E is NULL", fn);
+    if (typed && cosine && (reinterpret_cast<uintptr_t>(E) & 15u))
+        return fail(ctx, LWC_ERR_INVALID, "%s: E must be 16-byte aligned", fn);
+    if (d.M > 0 && (!V || !w)) return fail(ctx, LWC_ERR_INVALID, "%s: V or w is NULL with M > 0", fn);
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    if (d.memory == LWC_MEM_HOST) return score_host(ctx, d, pl, E, V, w, conf, cw, agree, winner, rank);
+    if (d.memory == LWC_MEM_HOST) return score_host(ctx, d, pl, e_type, E, V, w, conf, cw, agree, winner, rank);
 
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
     lwc::ScoreParams p;
-    p.E = E, p.V = V, p.w = w;
+    p.E = static_cast<const float *>(E), p.V = V, p.w = w;
     p.conf = conf, p.cw = cw, p.agree = agree, p.winner = winner, p.rank = rank;
     p.R = d.R, p.N = d.N, p.D = d.D, p.M = d.M;
     p.w_per_request = d.w_per_request;
-    p.cosine = d.similarity == LWC_SIM_COSINE ? 1 : 0;
+    p.cosine = cosine ? 1 : 0;
     p.inputs_resident = (ctx->flags & LWC_CTX_INPUTS_RESIDENT) ? 1 : 0;
-    return launch_plan(ctx, pl, p, stream ? static_cast<cudaStream_t>(stream) : ctx->stream);
+    if (typed && cosine) {
+        // device-resident f64 / bf16: converted into the context's conversion buffer on the same stream
+        const size_t n = (size_t)d.R * d.N * d.D;
+        if (n * sizeof(float) > ctx->typed_cap) {
+            if (ctx->typed_buf) CUDA_TRY(ctx, cudaFree(ctx->typed_buf));
+            ctx->typed_buf = nullptr, ctx->typed_cap = 0;
+            CUDA_TRY(ctx, cudaMalloc(&ctx->typed_buf, n * sizeof(float) + 256));
+            ctx->typed_cap = n * sizeof(float) + 256;
+        }
+        int rc = launch_convert(ctx, e_type, E, static_cast<float *>(ctx->typed_buf), n, st);
+        if (rc) return rc;
+        p.E = static_cast<const float *>(ctx->typed_buf);
+        p.inputs_resident = 0; // E was just produced on this stream: the score kernel's reads must wait for it
+    }
+    return launch_plan(ctx, pl, p, st);
+}
+
+int32_t lwc_score_batch(lwc_ctx *ctx, const lwc_batch_desc *desc, const float *E, const float *V, const float *w,
+                        float *conf, float *cw, float *agree, int32_t *winner, int32_t *rank, void *stream) {
+    return score_typed(ctx, "lwc_score_batch", desc, LWC_ELEM_F32, E, V, w, conf, cw, agree, winner, rank, stream);
+}
+
+int32_t lwc_score_batch_typed(lwc_ctx *ctx, const lwc_batch_desc *desc, int32_t e_type, const void *E, const float *V,
+                              const float *w, float *conf, float *cw, float *agree, int32_t *winner, int32_t *rank,
+                              void *stream) {
+    return score_typed(ctx, "lwc_score_batch_typed", desc, e_type, E, V, w, conf, cw, agree, winner, rank, stream);
+}
+
+int32_t lwc_score_batches(lwc_ctx *ctx, int32_t n_batches, const lwc_batch_desc *descs, const float *const *E,
+                          const float *const *V, const float *const *w, float *const *conf, float *const *cw,
+                          float *const *agree, int32_t *const *winner, int32_t *const *rank, void *stream) {
+    if (!ctx) return LWC_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (n_batches < 0 || (n_batches > 0 && !descs)) return fail(ctx, LWC_ERR_INVALID, "lwc_score_batches: bad batch list");
+    // validate everything first: either all batches are enqueued or none is
+    for (int32_t b = 0; b < n_batches; ++b) {
+        const lwc_batch_desc &d = descs[b];
+        if (d.memory != LWC_MEM_DEVICE)
+            return fail(ctx, LWC_ERR_INVALID, "lwc_score_batches: batch %d is not LWC_MEM_DEVICE (host batches are pipelined by lwc_score_batch)", b);
+        if (plan_for(d, E ? E[b] : nullptr).route == ROUTE_INVALID)
+            return fail(ctx, LWC_ERR_INVALID, "lwc_score_batches: batch %d has an invalid descriptor (R=%d N=%d D=%d M=%d)", b, d.R, d.N,
+                        d.D, d.M);
+        if (d.R > 0 && d.similarity == LWC_SIM_COSINE && (!E || !E[b]))
+            return fail(ctx, LWC_ERR_INVALID, "lwc_score_batches: batch %d: E is NULL", b);
+        if (d.R > 0 && d.M > 0 && (!V || !w || !V[b] || !w[b]))
+            return fail(ctx, LWC_ERR_INVALID, "lwc_score_batches: batch %d: V or w is NULL with M > 0", b);
+    }
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
+    for (int32_t b = 0; b < n_batches; ++b) {
+        const lwc_batch_desc &d = descs[b];
+        if (d.R == 0) continue;
+        const Plan pl = plan_for(d, E ? E[b] : nullptr);
+        lwc::ScoreParams p;
+        p.E = E ? E[b] : nullptr, p.V = V ? V[b] : nullptr, p.w = w ? w[b] : nullptr;
+        p.conf = conf ? conf[b] : nullptr, p.cw = cw ? cw[b] : nullptr, p.agree = agree ? agree[b] : nullptr;
+        p.winner = winner ? winner[b] : nullptr, p.rank = rank ? rank[b] : nullptr;
+        p.R = d.R, p.N = d.N, p.D = d.D, p.M = d.M;
+        p.w_per_request = d.w_per_request;
+        p.cosine = d.similarity == LWC_SIM_COSINE ? 1 : 0;
+        p.inputs_resident = (ctx->flags & LWC_CTX_INPUTS_RESIDENT) ? 1 : 0;
+        const int rc = launch_plan(ctx, pl, p, st);
+        if (rc) return rc;
+    }
+    return LWC_OK;
 }
 
 int32_t lwc_merge_error_codes(const uint16_t *codes, int32_t n_voters) {
@@ -633,9 +794,15 @@ int32_t lwc_vote_from_logprobs(lwc_ctx *ctx, int32_t n_rows, int32_t n_top, int3
         dV = static_cast<float *>(s.buf[3]);
     }
     const size_t tile = lwc::vote_tile_smem(n_top, n_choices);
-    if (tile <= 48 * 1024) {
-        lwc::vote_tile_kernel<<<(n_rows + lwc::kVoteRows - 1) / lwc::kVoteRows, lwc::kVoteRows, tile, st>>>(dlp, dlf, dV, n_rows,
-                                                                                                            n_top, n_choices);
+    const size_t tile4 = lwc::vote_tile4_smem(n_top, n_choices);
+    const bool vec4 = n_top >= 4 && n_top % 4 == 0 && tile4 <= 48 * 1024 &&
+                      ((reinterpret_cast<uintptr_t>(dlp) | reinterpret_cast<uintptr_t>(dlf)) & 15u) == 0;
+    const unsigned tiles = (unsigned)((n_rows + lwc::kVoteRows - 1) / lwc::kVoteRows);
+    if (vec4) {
+        lwc::vote_tile4_kernel<<<tiles, lwc::kVoteRows, tile4, st>>>(dlp, dlf, dV, n_rows, n_top, n_choices,
+                                                                    lwc::vote_tile4_pitch4(n_top));
+    } else if (tile <= 48 * 1024) {
+        lwc::vote_tile_kernel<<<tiles, lwc::kVoteRows, tile, st>>>(dlp, dlf, dV, n_rows, n_top, n_choices);
     } else {
         const int warps = 4;
         lwc::vote_from_logprobs_kernel<<<(n_rows + warps - 1) / warps, warps * 32, 0, st>>>(dlp, dlf, dV, n_rows, n_top,
@@ -652,16 +819,19 @@ int32_t lwc_vote_from_logprobs(lwc_ctx *ctx, int32_t n_rows, int32_t n_top, int3
 
 int32_t lwc_stage_f64(lwc_ctx *ctx, const double *src, size_t n, float *dst) {
     if (n && (!src || !dst)) return fail(ctx, LWC_ERR_INVALID, "lwc_stage_f64: NULL argument");
-    // one embedding (a few thousand values) converts inline; a whole batch is split over host threads so the
-    // conversion keeps up with the PCIe copy that follows it
+    // one embedding (a few thousand values) converts inline -- this is the per-row call of the request packers, so
+    // nothing but the loop runs; a whole batch is split over host threads so that the conversion keeps up with the
+    // PCIe copy that follows it
     const size_t kPerThread = (size_t)1 << 20;
+    if (n <= kPerThread) {
+        lwc_host::convert_f64_f32(src, n, dst);
+        return LWC_OK;
+    }
     unsigned nt = (unsigned)((n + kPerThread - 1) / kPerThread);
-    const unsigned hw = std::thread::hardware_concurrency();
+    static const unsigned hw = std::thread::hardware_concurrency();
     if (nt > (hw ? hw : 1u)) nt = hw ? hw : 1u;
     if (nt > 16u) nt = 16u;
-    auto convert = [src, dst](size_t a, size_t b) {
-        for (size_t i = a; i < b; ++i) dst[i] = static_cast<float>(src[i]);
-    };
+    auto convert = [src, dst](size_t a, size_t b) { lwc_host::convert_f64_f32(src + a, b - a, dst + a); };
     if (nt <= 1) {
         convert(0, n);
         return LWC_OK;
@@ -672,6 +842,14 @@ int32_t lwc_stage_f64(lwc_ctx *ctx, const double *src, size_t n, float *dst) {
     for (unsigned t = 1; t < nt; ++t) pool.emplace_back(convert, std::min(n, t * per), std::min(n, (t + 1) * per));
     convert(0, std::min(n, per));
     for (auto &th : pool) th.join();
+    return LWC_OK;
+}
+
+int32_t lwc_stage_f64_bf16(lwc_ctx *ctx, const double *src, size_t n, uint16_t *dst) {
+    if (n && (!src || !dst)) return fail(ctx, LWC_ERR_INVALID, "lwc_stage_f64_bf16: NULL argument");
+    // f64 -> fp32 (nearest even) -> bf16 (nearest even); NaN stays NaN.  The double rounding differs from a direct
+    // f64 -> bf16 rounding only on exact fp32 ties, far below the format's 2^-9 resolution.
+    lwc_host::convert_f64_bf16(src, n, dst);
     return LWC_OK;
 }
 

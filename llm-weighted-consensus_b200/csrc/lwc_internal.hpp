@@ -63,6 +63,12 @@ struct lwc_ctx {
     size_t table_cap[5] = {0};
     long long table_rows = 0;
     int table_D = 0, table_M = 0;
+    void *typed_buf = nullptr; // fp32 copy of device-resident f64 / bf16 embeddings (lwc_score_batch_typed)
+    size_t typed_cap = 0;
+    void *tc_flags = nullptr;  // per-request fix-up marks of the fp16-piece tcgen05 route (score_tc16.cuh)
+    size_t tc_flags_cap = 0;
+    int small_x3_tf32 = 0;     // LWC_SMALL_X3=tf32: the one-CTA-per-request fp32-grade kernel on tf32 pieces
+    int tc_x3_tf32 = 0;        // LWC_TC_X3=tf32: fp32-grade large pools on tf32 pieces (score_tc_kernel<true>) only
     int tc_ko = 0;     // operand slabs per stage of the tcgen05 kernel (LWC_TC_KO)
     int tc_stages = 0; // its ring depth (LWC_TC_STAGES)
 };
@@ -86,5 +92,9 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn encode_tiled_fn();
+
+// host_convert.cpp: vectorised element conversion of embedding rows
+void convert_f64_f32(const double *src, size_t n, float *dst);
+void convert_f64_bf16(const double *src, size_t n, uint16_t *dst);
 
 } // namespace lwc_host

@@ -3,6 +3,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 #include "lwc_internal.hpp"
@@ -22,6 +23,58 @@ int table_ensure(lwc_ctx *ctx, int which, size_t bytes) {
     return LWC_OK;
 }
 
+// Host -> device upload of a large, possibly pageable array.  cudaMemcpy from pageable memory goes through the
+// driver's single staging buffer (measured: 11 GB/s, 0.55 s for a 6.1 GB table); here host threads copy 32 MiB
+// pieces into two pinned buffers while the previous piece crosses PCIe.  Memory that is already pinned
+// (lwc_host_alloc, cudaHostRegister) is copied directly.
+int upload_staged(lwc_ctx *ctx, void *dst, const void *src, size_t bytes) {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        return LWC_OK;
+    }
+    cudaGetLastError();
+    const size_t piece = (size_t)32 << 20;
+    if (bytes <= piece) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream)); // pageable source: the caller may reuse it after the call
+        return LWC_OK;
+    }
+    void *pin[2] = {nullptr, nullptr};
+    cudaEvent_t done[2] = {nullptr, nullptr};
+    int rc = LWC_OK;
+    for (int i = 0; i < 2 && !rc; ++i)
+        if (cudaHostAlloc(&pin[i], piece, cudaHostAllocDefault) != cudaSuccess ||
+            cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming) != cudaSuccess)
+            rc = fail(ctx, LWC_ERR_INTERNAL, "lwc_table_load: pinned staging allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+    const unsigned hw = std::thread::hardware_concurrency();
+    const unsigned nt = hw >= 8 ? 4 : (hw >= 2 ? 2 : 1);
+    size_t off = 0;
+    for (int k = 0; !rc && off < bytes; ++k, off += piece) {
+        const int b = k & 1;
+        const size_t n = bytes - off < piece ? bytes - off : piece;
+        if (k >= 2 && cudaEventSynchronize(done[b]) != cudaSuccess) rc = fail(ctx, LWC_ERR_INTERNAL, "lwc_table_load: staging wait failed");
+        if (rc) break;
+        std::vector<std::thread> th;
+        const size_t per = (n + nt - 1) / nt;
+        const char *s = static_cast<const char *>(src) + off;
+        char *d = static_cast<char *>(pin[b]);
+        for (unsigned t = 1; t < nt; ++t)
+            if (t * per < n) th.emplace_back([=] { memcpy(d + t * per, s + t * per, std::min(per, n - t * per)); });
+        memcpy(d, s, std::min(per, n));
+        for (auto &x : th) x.join();
+        if (cudaMemcpyAsync(static_cast<char *>(dst) + off, pin[b], n, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess ||
+            cudaEventRecord(done[b], ctx->stream) != cudaSuccess)
+            rc = fail(ctx, LWC_ERR_INTERNAL, "lwc_table_load: staged copy failed: %s", cudaGetErrorString(cudaGetLastError()));
+    }
+    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess && !rc) rc = fail(ctx, LWC_ERR_INTERNAL, "lwc_table_load: upload failed");
+    for (int i = 0; i < 2; ++i) {
+        if (done[i]) cudaEventDestroy(done[i]);
+        if (pin[i]) cudaFreeHost(pin[i]);
+    }
+    return rc;
+}
+
 } // namespace
 
 extern "C" {
@@ -37,8 +90,8 @@ int32_t lwc_table_load(lwc_ctx *ctx, const float *T, const float *Q, int64_t row
     if ((rc = table_ensure(ctx, 0, (size_t)rows * D * 4))) return rc;
     if ((rc = table_ensure(ctx, 1, (size_t)rows * 4))) return rc;
     if ((rc = table_ensure(ctx, 2, (size_t)rows * M * 4))) return rc;
-    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->table_buf[0], T, (size_t)rows * D * 4, cudaMemcpyHostToDevice, ctx->stream));
-    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->table_buf[2], Q, (size_t)rows * M * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if ((rc = upload_staged(ctx, ctx->table_buf[0], T, (size_t)rows * D * 4))) return rc;
+    if ((rc = upload_staged(ctx, ctx->table_buf[2], Q, (size_t)rows * M * 4))) return rc;
     const int warps = 8;
     lwc::table_norm_kernel<<<(unsigned)((rows + warps - 1) / warps), warps * 32, 0, ctx->stream>>>(
         static_cast<const float *>(ctx->table_buf[0]), static_cast<float *>(ctx->table_buf[1]), rows, D);

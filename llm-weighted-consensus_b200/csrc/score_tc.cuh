@@ -146,7 +146,9 @@ __device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 1, 128;" :::
 
 template <bool X3>
 __global__ void __launch_bounds__(X3 ? kTcThreadsX3 : kTcThreads, 1)
-score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, const TcGeom geo) {
+score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, const TcGeom geo, const int *__restrict__ fix_flags) {
+    // fix_flags != nullptr: fix-up pass behind score_tc16_kernel (score_tc16.cuh) -- only the requests it marked are
+    // scored here; every role skips the others, so the pipelines stay in step
     extern __shared__ __align__(1024) unsigned char smem_tc[];
     const int KO = geo.ko, S = geo.stages;
     // TF32 route: a stage is one TMA box of KO slabs.  X3: a stage is KO pairs [raw slab][lo slab], each pair
@@ -221,7 +223,8 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
             const uint32_t ring_u32 = smem_u32(ring);
             int slot = 0;
             uint32_t phase = 0;
-            for (int q = 0; q < nreq; ++q)
+            for (int q = 0; q < nreq; ++q) {
+                if (fix_flags && !__ldg(fix_flags + r_begin + q)) continue;
                 for (int s = 0; s < spr; ++s) {
                     mbar_wait_backoff(empty0 + 8 * slot, phase ^ 1u, 40);
                     if (X3) { // one box per slab, into the first half of its [raw][lo] pair
@@ -239,6 +242,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                         phase ^= 1u;
                     }
                 }
+            }
         }
         __syncwarp();
     } else if (warp == 1) {
@@ -250,16 +254,19 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
             int slot = 0;
             uint32_t phase = 0;
             uint32_t tile = 0; // accumulator hand-offs so far: one per request (TF32) or per chunk (X3)
+            uint32_t nproc = 0; // requests scored so far by this CTA
             for (int q = 0; q < nreq; ++q) {
+                if (fix_flags && !__ldg(fix_flags + r_begin + q)) continue;
                 uint32_t ab = tile & 1u;
                 mbar_wait(tempty0 + 8 * ab, ((tile >> 1) & 1u) ^ 1u); // accumulator drained by the epilogue
                 tc_fence_after();
                 uint32_t d_tmem = tmem_base + ab * kAccCols;
                 uint32_t acc = 0;
                 if (X3) { // both Y halves drained and zeroed by the epilogue of the previous request
-                    mbar_wait(yempty0, ((uint32_t)q & 1u) ^ 1u);
+                    mbar_wait(yempty0, (nproc & 1u) ^ 1u);
                     tc_fence_after();
                 }
+                ++nproc;
                 for (int s = 0; s < spr; ++s) {
                     if (X3 && s > 0 && s % cst == 0) { // chunk boundary: hand over, switch accumulator
                         umma_commit(tfull0 + 8 * ab);
@@ -301,7 +308,8 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         const int tw = warp < 4 ? warp - 2 : warp - 6; // 0..3
         int slot = 0;
         uint32_t phase = 0;
-        for (int q = 0; q < nreq; ++q)
+        for (int q = 0; q < nreq; ++q) {
+            if (fix_flags && !__ldg(fix_flags + r_begin + q)) continue;
             for (int s = 0; s < spr; ++s) {
                 mbar_wait_backoff(full0 + 8 * slot, phase, 40);
                 const int nk = min(KO, nslab - s * KO);
@@ -331,6 +339,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                     phase ^= 1u;
                 }
             }
+        }
     } else if (warp >= 4 && warp < 8) {
         // ===================== epilogue =====================
         const int i = threadIdx.x - 128;   // row of S owned by this thread == TMEM lane
@@ -341,6 +350,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         const int nchunk = X3 ? (spr + cst - 1) / cst : 1;
         for (int q = 0; q < nreq; ++q) {
             const int r = r_begin + q;
+            if (fix_flags && !__ldg(fix_flags + r)) continue;
             const float *Vr = p.V + (size_t)r * M * N;
             const float *wr = p.w + (p.w_per_request ? (size_t)r * M : 0);
             // t_i = sum_m w_m V_mi (client.rs:410-415): independent of E, overlaps the MMAs.  Eight voters' loads are

@@ -10,11 +10,12 @@ import os
 import numpy as np
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_PKG, "liblwc_b200.so")
+LIB_PATH = os.environ.get("LWC_B200_LIB") or os.path.join(_PKG, "liblwc_b200.so")  # override: A/B builds of the same ABI
 
 SIM_IDENTITY, SIM_COSINE = 0, 1
 PREC_FP32, PREC_TF32X3, PREC_TF32, PREC_BF16 = 0, 1, 2, 3
 MEM_HOST, MEM_DEVICE = 0, 1
+ELEM_F32, ELEM_F64, ELEM_BF16 = 0, 1, 2
 MAX_CHOICES, MAX_VOTERS = 128, 128
 CTX_INPUTS_RESIDENT = 1
 
@@ -76,6 +77,12 @@ def load_library():
     L.lwc_stream_synchronize.restype = i32
     L.lwc_score_batch.argtypes = [vp, ctypes.POINTER(BatchDesc)] + [vp] * 9
     L.lwc_score_batch.restype = i32
+    L.lwc_score_batch_typed.argtypes = [vp, ctypes.POINTER(BatchDesc), i32] + [vp] * 9
+    L.lwc_score_batch_typed.restype = i32
+    L.lwc_stage_f64_bf16.argtypes = [vp, vp, ctypes.c_size_t, vp]
+    L.lwc_stage_f64_bf16.restype = i32
+    L.lwc_score_batches.argtypes = [vp, i32, ctypes.POINTER(BatchDesc)] + [vp] * 9
+    L.lwc_score_batches.restype = i32
     L.lwc_kernel_for.argtypes = [vp, ctypes.POINTER(BatchDesc)]
     L.lwc_kernel_for.restype = ctypes.c_char_p
     L.lwc_launch_count.argtypes = [vp]
@@ -247,6 +254,26 @@ class Context:
         self._check(self.lib.lwc_score_batch(self.handle, ctypes.byref(desc), vp(E), vp(V), vp(w), vp(conf), vp(cw),
                                              vp(agree), vp(winner), vp(rank), vp(stream)))
 
+    def batch_list(self, descs, E, V, w, conf, cw, agree, winner, rank, stream=None):
+        """Pre-builds the argument arrays of lwc_score_batches (device pointers as ints, None allowed) and returns a
+        zero-argument callable that enqueues the whole list; the arrays stay alive with the callable."""
+        n = len(descs)
+        darr = (BatchDesc * n)(*descs)
+
+        def parr(ptrs):
+            if ptrs is None:
+                return None
+            return (ctypes.c_void_p * n)(*[ctypes.c_void_p(x) if x is not None else None for x in ptrs])
+
+        arrays = [parr(a) for a in (E, V, w, conf, cw, agree, winner, rank)]
+        st = ctypes.c_void_p(stream) if stream else None
+
+        def call():
+            self._check(self.lib.lwc_score_batches(self.handle, n, darr, *arrays, st))
+
+        call.keepalive = (darr, arrays)
+        return call
+
     def score_batch(self, E, V, w, similarity=SIM_COSINE, precision=PREC_FP32, outputs=("conf", "cw", "agree", "winner", "rank")):
         """Host-memory call: numpy in, numpy out (lwc_score_batch with LWC_MEM_HOST)."""
         V = np.ascontiguousarray(V, dtype=np.float32)
@@ -300,6 +327,42 @@ class Context:
             return {"conf": dconf.download((R, N), np.float32), "cw": dcw.download((R, N), np.float32),
                     "agree": dag.download((R, M), np.float32), "winner": dwin.download((R,), np.int32),
                     "rank": drk.download((R, N), np.int32)}
+        finally:
+            for b in bufs:
+                b.free()
+
+    def stage_f64_bf16(self, src):
+        """lwc_stage_f64_bf16: float64 array -> uint16 array of bf16 bit patterns."""
+        src = np.ascontiguousarray(src, dtype=np.float64)
+        dst = np.empty(src.shape, np.uint16)
+        self._check(self.lib.lwc_stage_f64_bf16(self.handle, _np_ptr(src), src.size, _np_ptr(dst)))
+        return dst
+
+    def score_batch_typed(self, E, e_type, V, w, precision=PREC_FP32, memory=MEM_HOST):
+        """lwc_score_batch_typed: E is float64 (ELEM_F64) or uint16 bf16 bits (ELEM_BF16), host or device memory."""
+        E = np.ascontiguousarray(E, dtype=np.float64 if e_type == ELEM_F64 else (np.uint16 if e_type == ELEM_BF16 else np.float32))
+        V = np.ascontiguousarray(V, dtype=np.float32)
+        w = np.ascontiguousarray(w, dtype=np.float32)
+        R, M, N = V.shape
+        D = E.shape[2]
+        desc = BatchDesc(R, N, D, M, SIM_COSINE, precision, memory, 1 if w.ndim == 2 else 0)
+        shapes = {"conf": ((R, N), np.float32), "cw": ((R, N), np.float32), "agree": ((R, M), np.float32),
+                  "winner": ((R,), np.int32), "rank": ((R, N), np.int32)}
+        vp = ctypes.c_void_p
+        if memory == MEM_HOST:
+            out = {k: np.zeros(sh, t) for k, (sh, t) in shapes.items()}
+            self._check(self.lib.lwc_score_batch_typed(self.handle, ctypes.byref(desc), e_type, _np_ptr(E), _np_ptr(V), _np_ptr(w),
+                                                       *[_np_ptr(out[k]) for k in shapes], None))
+            return out
+        bufs = []
+        try:
+            ins = [DeviceBuffer(self, max(a.nbytes, 4)).upload(a) for a in (E, V, w)]
+            outs = {k: DeviceBuffer(self, int(np.prod(sh)) * 4 + 4) for k, (sh, t) in shapes.items()}
+            bufs = ins + list(outs.values())
+            self._check(self.lib.lwc_score_batch_typed(self.handle, ctypes.byref(desc), e_type, *[vp(b.ptr) for b in ins],
+                                                       *[vp(outs[k].ptr) for k in shapes], None))
+            self.synchronize()
+            return {k: outs[k].download(sh, t) for k, (sh, t) in shapes.items()}
         finally:
             for b in bufs:
                 b.free()

@@ -85,6 +85,35 @@ extern "C" {
         rank: *mut i32,
         stream: *mut c_void,
     ) -> i32;
+    pub fn lwc_score_batch_typed(
+        ctx: *mut lwc_ctx,
+        desc: *const lwc_batch_desc,
+        e_type: i32,
+        E: *const c_void,
+        V: *const f32,
+        w: *const f32,
+        conf: *mut f32,
+        cw: *mut f32,
+        agree: *mut f32,
+        winner: *mut i32,
+        rank: *mut i32,
+        stream: *mut c_void,
+    ) -> i32;
+    pub fn lwc_stage_f64_bf16(ctx: *mut lwc_ctx, src: *const f64, n: usize, dst: *mut u16) -> i32;
+    pub fn lwc_score_batches(
+        ctx: *mut lwc_ctx,
+        n_batches: i32,
+        descs: *const lwc_batch_desc,
+        E: *const *const f32,
+        V: *const *const f32,
+        w: *const *const f32,
+        conf: *const *mut f32,
+        cw: *const *mut f32,
+        agree: *const *mut f32,
+        winner: *const *mut i32,
+        rank: *const *mut i32,
+        stream: *mut c_void,
+    ) -> i32;
     pub fn lwc_kernel_for(ctx: *const lwc_ctx, desc: *const lwc_batch_desc) -> *const c_char;
     pub fn lwc_launch_count(ctx: *const lwc_ctx) -> u64;
     pub fn lwc_merge_error_codes(codes: *const u16, n_voters: i32) -> i32;

@@ -191,7 +191,13 @@ where
             _ => 1,
         };
         let prompt: Vec<f32> = embeddings_response.data.first().map(|e| e.embedding.iter().map(|&x| x as f32).collect()).unwrap_or_default();
-        let weights = self.ctx.table_weights(&prompt, top, &col(0), &col(1), &col(2))?;
+        // lwc_table_weights(LWC_MEM_HOST) blocks until the weights are home (a table scan of ~1 ms plus copies): it must
+        // not run on a tokio worker.  The blocking pool takes it; the C++ twin (lwc_host.hpp) goes one step further and
+        // lets a worker thread gather concurrent prompts into one call.
+        let (ctx, base, min, max) = (self.ctx.clone(), col(0), col(1), col(2));
+        let weights = tokio::task::spawn_blocking(move || ctx.table_weights(&prompt, top, &base, &min, &max))
+            .await
+            .map_err(|e| ResponseError { code: 500, message: serde_json::Value::String(format!("table lookup task failed: {e}")) })??;
         let weights = weights.into_iter().map(|w| Decimal::from_f32(w).unwrap_or(Decimal::ONE)).collect();
         Ok((weights, score::completions::weight::TrainingTableData { embeddings_response }))
     }

@@ -101,6 +101,88 @@ static int cpu_checks() {
     REQUIRE(!agg.choices[3].confidence.has_value()); // no vote: untouched (client.rs:440)
     for (const auto &ch : agg.choices)
         REQUIRE(!ch.delta.content && !ch.delta.vote && !ch.finish_reason && !ch.error); // client.rs:451-454
+    // ---- candidate sources: a multichat completion's generations become the candidates of a score request, and the
+    // candidate order (= row order of E) is the request's choice order (request.rs:84-89, client.rs:144-170,1145-1152)
+    {
+        namespace rq = score::completions::request;
+        multichat::completions::response::unary::ChatCompletion mc;
+        mc.id = "mc-1";
+        for (uint64_t i = 0; i < 4; ++i) {
+            multichat::completions::response::unary::Choice c;
+            c.index = 3 - i; // stored out of order: lookup is by `index`, not by position
+            c.message.content = "answer " + std::to_string(3 - i);
+            if (3 - i == 1) c.message.reasoning = "because";
+            if (3 - i == 2) c.error = error::ResponseError(500, "generation failed");
+            mc.choices.push_back(c);
+        }
+        rq::MultichatArchive archive{{mc.id, mc}};
+        std::vector<rq::Choice> choices = rq::choices_from_multichat(mc); // failed generation 2 is left out
+        REQUIRE(choices.size() == 3);
+        choices.push_back(rq::Choice::Text("a literal candidate"));
+        const auto internal = rq::convert_choices_to_internal_choices(archive, choices);
+        const auto texts = rq::choice_texts(internal);
+        REQUIRE(texts.size() == 4);
+        REQUIRE(texts[0] == "answer 3" && texts[1] == "because\n\nanswer 1" && texts[2] == "answer 0");
+        REQUIRE(texts[3] == "a literal candidate");
+        REQUIRE(internal[1].multichat_choice.index == 1);
+        try {
+            rq::convert_choices_to_internal_choices(archive, {rq::Choice::MultichatCompletion("mc-1", 9)});
+            REQUIRE(false);
+        } catch (const error::ResponseError &e) { // Error::InvalidCompletionChoiceIndex -> 400 (error.rs:43)
+            REQUIRE(e.code == 400 && e.message.find("invalid choice_index for completion mc-1: 9") != std::string::npos);
+        }
+    }
+    // ---- the host half of get_vote's numeric tail (client.rs:1766-1784): which alternatives reach the device
+    {
+        using chat::completions::response::TopLogprob;
+        std::vector<TopLogprob> alts = {{"`B", -0.1}, {"`A", -2.5}, {"`", -3.0}, {"`Z", -1.0}, {"`C", std::nullopt}, {"\xc3\xa9" "A", -0.5}};
+        auto leaf_of = [](char c) -> std::optional<int32_t> { // lowest branch holds the leaves A, B, C -> choices 4, 7, 2
+            if (c == 'A') return 4;
+            if (c == 'B') return 7;
+            if (c == 'C') return 2;
+            return std::nullopt;
+        };
+        float lp[8];
+        int32_t leaf[8];
+        score::completions::fill_vote_pairs(alts, 1, leaf_of, 8, lp, leaf);
+        REQUIRE(leaf[0] == 7 && lp[0] == -0.1f);
+        REQUIRE(leaf[1] == 4 && lp[1] == -2.5f);
+        REQUIRE(leaf[2] == -1);            // token too short
+        REQUIRE(leaf[3] == -1);            // 'Z' is no sibling leaf
+        REQUIRE(leaf[4] == -1);            // logprob None
+        REQUIRE(leaf[5] == -1);            // byte 1 is inside a multi-byte char
+        REQUIRE(leaf[6] == -1 && leaf[7] == -1 && std::isnan(lp[7])); // padding
+    }
+    // ---- weight::Fetchers dispatch (weight.rs:45-63) with the static fetcher (weight.rs:76-97)
+    {
+        namespace wt = score::completions::weight;
+        struct Ctx {};
+        struct Req {
+            std::string prompt;
+        };
+        score::model::Model model;
+        const double ws[3] = {1.0, 0.25, 2.5};
+        for (size_t i = 0; i < 3; ++i) {
+            score::model::Llm l;
+            l.id = "llm" + std::to_string(i);
+            l.index = i;
+            l.weight.weight = ws[i];
+            REQUIRE(!l.weight.validate().has_value());
+            model.llms.push_back(l);
+        }
+        wt::Fetchers<Ctx, Req> fetchers;
+        fetchers.static_ = std::make_shared<wt::StaticFetcher<Ctx, Req>>();
+        auto got = fetchers.fetch(Ctx{}, std::make_shared<const Req>(Req{"p"}), model);
+        REQUIRE(got.second.type == score::WeightType::Static);
+        REQUIRE(got.first.size() == 3 && got.first[0] == 1.0 && got.first[1] == 0.25 && got.first[2] == 2.5);
+        score::llm::Weight bad;
+        bad.weight = 0.0; // llm/mod.rs:650-660
+        REQUIRE(bad.validate().has_value());
+        bad = score::llm::Weight{};
+        bad.type = score::WeightType::TrainingTable;
+        bad.base_weight = 1.0, bad.min_weight = 2.0, bad.max_weight = 3.0; // base < min, llm/mod.rs:671-687
+        REQUIRE(bad.validate().has_value());
+    }
     return 0;
 }
 
@@ -203,6 +285,27 @@ static int gpu_checks() {
                 REQUIRE(b.rank[0] == b.winner);
             }
         }
+    // the element type on the wire is a batcher option: f64 (rounded on the device) must give the fp32 transport's
+    // bits, bf16 (opt-in) must stay within its stated 1e-2 of the top confidence
+    {
+        Batcher::Options o64 = opt, o16 = opt;
+        o64.transport = LWC_ELEM_F64;
+        o16.transport = LWC_ELEM_BF16;
+        Batcher b64(0, o64), b16(0, o16);
+        for (int t = 0; t < 2; ++t)
+            for (int i = 0; i < 30; ++i) {
+                if (!reqs[t][i].embeddings) continue;
+                const Tally &a = got[t][i];
+                const Tally x = b64.submit(reqs[t][i]).get(), y = b16.submit(reqs[t][i]).get();
+                REQUIRE(x.winner == a.winner && x.rank == a.rank);
+                double top = 0;
+                for (double c : a.confidence) top = std::max(top, std::fabs(c));
+                for (size_t k = 0; k < a.confidence.size(); ++k) {
+                    REQUIRE(x.confidence[k] == a.confidence[k] && x.weight[k] == a.weight[k]);
+                    REQUIRE(std::fabs(y.confidence[k] - a.confidence[k]) <= 1e-2 * top);
+                }
+            }
+    }
     // from streamed chunks to the written-back aggregate (client.rs:362, 384-456) with the tally on the GPU:
     // similarity = identity, so the expected numbers are the reference's own (golden K-style case)
     {
@@ -266,6 +369,79 @@ static int gpu_checks() {
         try {
             lim.min[0] = 5.0f; // min > base: the reference's validate() refuses it (llm/mod.rs:671-687)
             c.table_weights(q, 1, 4, lim);
+            REQUIRE(false);
+        } catch (const error::ResponseError &e) {
+            REQUIRE(e.code == 400);
+        }
+    }
+    // weight::Fetcher for WeightType::TrainingTable: 24 threads fetch at once; the worker batches their prompts into a
+    // few lwc_table_weights calls; every result equals the direct host call for the same prompt
+    {
+        namespace wt = score::completions::weight;
+        struct Ctx {};
+        struct Req {
+            std::vector<double> prompt_embedding; // what the embeddings service would return for the prompt
+        };
+        const int rows = 512, D = 64, M = 4, T2 = 24;
+        std::mt19937 g(17);
+        std::normal_distribution<float> nd;
+        std::uniform_real_distribution<float> ud(0.f, 1.f);
+        std::vector<float> Tt((size_t)rows * D), Q((size_t)rows * M);
+        for (auto &x : Tt) x = nd(g);
+        for (auto &x : Q) x = ud(g);
+        const Context &c = batcher.context();
+        c.table_load(Tt, Q, rows, D, M);
+        score::model::Model model;
+        model.weight.type = score::WeightType::TrainingTable;
+        model.weight.top = 8;
+        Context::TableLimits lim;
+        for (int m = 0; m < M; ++m) {
+            score::model::Llm l;
+            l.index = (size_t)m;
+            l.weight.type = score::WeightType::TrainingTable;
+            l.weight.base_weight = 1.0 + 0.5 * m, l.weight.min_weight = 0.5, l.weight.max_weight = 4.0;
+            model.llms.push_back(l);
+            lim.base.push_back((float)l.weight.base_weight), lim.min.push_back(0.5f), lim.max.push_back(4.0f);
+        }
+        std::atomic<int> embed_calls{0};
+        auto tt = std::make_shared<wt::B200TrainingTableFetcher<Ctx, Req>>(
+            c, D, [&](Ctx, const Req &r, const score::model::Model &) {
+                ++embed_calls;
+                embeddings::response::CreateEmbeddingResponse er;
+                er.data.resize(1);
+                er.data[0].embedding = r.prompt_embedding;
+                return er;
+            });
+        wt::Fetchers<Ctx, Req> fetchers;
+        fetchers.static_ = std::make_shared<wt::StaticFetcher<Ctx, Req>>();
+        fetchers.training_table = tt;
+        std::vector<std::shared_ptr<const Req>> rq2;
+        for (int t = 0; t < T2; ++t) {
+            Req r;
+            r.prompt_embedding.resize(D);
+            for (auto &x : r.prompt_embedding) x = nd(g);
+            rq2.push_back(std::make_shared<const Req>(std::move(r)));
+        }
+        std::vector<std::pair<std::vector<double>, wt::Data>> res(T2);
+        std::vector<std::thread> th2;
+        for (int t = 0; t < T2; ++t) th2.emplace_back([&, t] { res[t] = fetchers.fetch(Ctx{}, rq2[t], model); });
+        for (auto &x : th2) x.join();
+        REQUIRE(embed_calls == T2);
+        std::printf("table-weight calls: %llu for %d fetches\n", (unsigned long long)tt->calls(), T2);
+        REQUIRE(tt->calls() >= 1 && tt->calls() <= (uint64_t)T2);
+        for (int t = 0; t < T2; ++t) {
+            REQUIRE(res[t].second.type == score::WeightType::TrainingTable);
+            REQUIRE(res[t].second.training_table.embeddings_response.data[0].embedding == rq2[t]->prompt_embedding);
+            std::vector<float> q(rq2[t]->prompt_embedding.begin(), rq2[t]->prompt_embedding.end());
+            const std::vector<float> w = c.table_weights(q, 1, 8, lim);
+            REQUIRE(res[t].first.size() == (size_t)M);
+            for (int m = 0; m < M; ++m) REQUIRE((float)res[t].first[m] == w[m]);
+        }
+        // a model whose limits the reference's validate() refuses: the error arrives through the future as 400
+        score::model::Model badm = model;
+        badm.llms[0].weight.min_weight = 9.0;
+        try {
+            tt->fetch(Ctx{}, rq2[0], badm).get();
             REQUIRE(false);
         } catch (const error::ResponseError &e) {
             REQUIRE(e.code == 400);

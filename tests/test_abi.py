@@ -95,3 +95,27 @@ def test_stage_f64_is_a_host_function_and_rounds_like_a_cast(lwc):
         assert rc == 0
         assert (dst[:n] == src.astype(np.float32)).all() and dst[n] == 7.0
     assert L.lwc_stage_f64(None, None, 4, None) == 400
+
+
+def test_host_staging_conversions_without_a_gpu(lwc):
+    """lwc_stage_f64 / lwc_stage_f64_bf16 are host-only loops (vectorised when the CPU has AVX2): every length,
+    special values and rounding ties against numpy models."""
+    L = lwc.load_library()
+    rng = np.random.default_rng(3)
+    for n in (0, 1, 7, 8, 9, 1536, 4097):
+        src = rng.standard_normal(n) * 10.0 ** rng.integers(-30, 30, n)
+        if n >= 9:
+            src[:9] = [np.nan, np.inf, -np.inf, 0.0, -0.0, 1e-45, 1.0 + 2.0 ** -9, 1.0 + 3 * 2.0 ** -9, 3.4e38]
+        f32 = np.full(n, 7.0, np.float32)
+        assert L.lwc_stage_f64(None, ctypes.c_void_p(src.ctypes.data), n, ctypes.c_void_p(f32.ctypes.data)) == 0
+        with np.errstate(over="ignore"):
+            want = src.astype(np.float32)
+        assert np.array_equal(f32, want, equal_nan=True)
+        bf = np.zeros(n, np.uint16)
+        assert L.lwc_stage_f64_bf16(None, ctypes.c_void_p(src.ctypes.data), n, ctypes.c_void_p(bf.ctypes.data)) == 0
+        u = want.view(np.uint32).astype(np.uint64)
+        model = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
+        nan = np.isnan(want)
+        assert np.array_equal(bf[~nan], model[~nan])
+        back = (bf.astype(np.uint32) << 16).view(np.float32)
+        assert np.all(np.isnan(back[nan]))

@@ -252,7 +252,7 @@ def test_cfg3_shape_slice(ctx, lwc, oracle):
     _, N, D, M = synth.CONFIGS["cfg3"]
     R = 300
     E, V, w, kinds = synth.make_batch(R, N, D, M, seed=3)
-    assert ctx.kernel_for(R, N, D, M) == "small32_tf32x3"
+    assert ctx.kernel_for(R, N, D, M) == "small32_f16x2"
     got = ctx.score_batch(E, V, w)
     properties_hold(got, V)
     want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
@@ -265,7 +265,7 @@ def test_cfg4_shape_slice(ctx, lwc, oracle):
     _, N, D, M = synth.CONFIGS["cfg4"]
     R = 24
     E, V, w, kinds = synth.make_batch(R, N, D, M, seed=4)
-    assert ctx.kernel_for(R, N, D, M) == "tc128_tf32x3"  # fp32-grade on tcgen05: tf32 product + bf16 correction product
+    assert ctx.kernel_for(R, N, D, M) == "tc128_f16x2"  # fp32-grade on tcgen05: two fp16-piece products per K step (score_tc16.cuh)
     got = ctx.score_batch(E, V, w)
     properties_hold(got, V)
     want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
@@ -286,7 +286,7 @@ def test_large_pool_fp32_grade_error_margin(ctx, lwc, oracle, D, positive):
     V = rng.random((R, M, N)).astype(np.float32) ** 4
     V /= V.sum(axis=2, keepdims=True)
     w = (rng.random((R, M)) + 0.5).astype(np.float32)
-    assert ctx.kernel_for(R, N, D, M) == "tc128_tf32x3"
+    assert ctx.kernel_for(R, N, D, M) == "tc128_f16x2"
     got = ctx.score_batch(E, V, w)
     want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
     # fraction of the stated tolerance (1e-5 relative + 1e-7 absolute, parity_util) that is used up
@@ -381,12 +381,12 @@ def test_large_pool_tcgen05_route(ctx, lwc, oracle, shape, memory):
 
 @pytest.mark.parametrize("shape", TC_SHAPES + [(3, 128, 32, 2), (4, 77, 160, 5)], ids=lambda s: "R%d_N%d_D%d_M%d" % s)
 def test_large_pool_tcgen05_fp32_grade_route(ctx, lwc, oracle, shape):
-    """The same shapes at the default precision: tf32 product + bf16 correction product, within the fp32 bar.
-    D = 32, 96 and 160 leave the last stage / the last bf16 slab half filled."""
+    """The same shapes at the default precision: the fp16-piece route (X + 2^-11 (Y + Y^T)), within the fp32 bar.
+    D = 32, 96 and 160 leave the last 64-column unit half filled (zero-filled by the TMA box)."""
     from lwc_b200 import synth
 
     R, N, D, M = shape
-    assert ctx.kernel_for(R, N, D, M) == "tc128_tf32x3"
+    assert ctx.kernel_for(R, N, D, M) == "tc128_f16x2"
     E, V, w, _ = synth.make_batch(R, N, D, M, seed=777 + N + D, edge_cases=False)
     if R > 3:
         V[1] = np.nan

@@ -64,7 +64,7 @@ TC_REGIME = [(600, 128, 3072, 16), (600, 128, 2304, 16), (600, 40, 3072, 16), (6
 @pytest.mark.parametrize("shape", TC_REGIME, ids=lambda s: "R%d_N%d_D%d_M%d" % s)
 def test_tcgen05_fp32_grade_many_requests_per_cta(ctx, lwc, oracle, shape):
     R, N, D, M = shape
-    assert ctx.kernel_for(R, N, D, M) == "tc128_tf32x3"
+    assert ctx.kernel_for(R, N, D, M) == "tc128_f16x2"
     E, V, w = fast_batch(R, N, D, M, seed=90 + N + D)
     got = ctx.score_batch_device(E, V, w)
     want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
@@ -162,3 +162,197 @@ def test_generic_route_many_requests(ctx, lwc, oracle):
         got = ctx.score_batch_device(E, V, w)
         want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
         assert compare(got, want, V) == 1.0
+
+
+def test_batch_list_entry_is_bit_equal_to_single_calls(lwc, oracle):
+    """lwc_score_batches enqueues a list of device-resident batches inside one call; the results must be the
+    bits of the same batches scored one lwc_score_batch call at a time -- with and without overlapped launches."""
+    shapes = [(700, 16, 1536, 4), (300, 32, 1024, 4), (40, 128, 512, 8), (0, 16, 64, 2), (90, 10, 50, 3), (700, 16, 1536, 4)]
+    batches = [fast_batch(max(R, 1), N, D, M, seed=50 + i)[:3] for i, (R, N, D, M) in enumerate(shapes)]
+    for flags in (0, lwc.CTX_INPUTS_RESIDENT):
+        with lwc.Context(device=0, flags=flags) as c:
+            singles, keep, descs, ptrs = [], [], [], {k: [] for k in ("E", "V", "w", "conf", "cw", "agree", "winner", "rank")}
+            for (R, N, D, M), (E, V, w) in zip(shapes, batches):
+                E, V, w = E[:R], V[:R], w[:R]
+                singles.append(c.score_batch_device(E, V, w) if R else None)
+                bufs = {"E": lwc.DeviceBuffer(c, max(E.nbytes, 4)).upload(E), "V": lwc.DeviceBuffer(c, max(V.nbytes, 4)).upload(V),
+                        "w": lwc.DeviceBuffer(c, max(w.nbytes, 4)).upload(w), "conf": lwc.DeviceBuffer(c, 4 * R * N + 4),
+                        "cw": lwc.DeviceBuffer(c, 4 * R * N + 4), "agree": lwc.DeviceBuffer(c, 4 * R * M + 4),
+                        "winner": lwc.DeviceBuffer(c, 4 * R + 4), "rank": lwc.DeviceBuffer(c, 4 * R * N + 4)}
+                keep.append(bufs)
+                descs.append(lwc.BatchDesc(R, N, D, M, lwc.SIM_COSINE, lwc.PREC_FP32, lwc.MEM_DEVICE, 1))
+                for k in ptrs:
+                    ptrs[k].append(bufs[k].ptr)
+            run = c.batch_list(descs, ptrs["E"], ptrs["V"], ptrs["w"], ptrs["conf"], ptrs["cw"], ptrs["agree"], ptrs["winner"],
+                               ptrs["rank"])
+            launches0 = c.launch_count()
+            run()
+            c.synchronize()
+            # one launch per non-empty batch; the fp32-grade tcgen05 route is two (fp16-piece pass + its fix-up pass)
+            assert c.launch_count() - launches0 == sum((2 if s[1] > 32 else 1) for s in shapes if s[0] > 0)
+            for (R, N, D, M), bufs, want in zip(shapes, keep, singles):
+                if not R:
+                    continue
+                got = {"conf": bufs["conf"].download((R, N), np.float32), "cw": bufs["cw"].download((R, N), np.float32),
+                       "agree": bufs["agree"].download((R, M), np.float32), "winner": bufs["winner"].download((R,), np.int32),
+                       "rank": bufs["rank"].download((R, N), np.int32)}
+                for k in got:
+                    assert np.array_equal(got[k], want[k], equal_nan=True), (k, (R, N, D, M), flags)
+            # a list with one bad entry enqueues nothing
+            bad = list(descs)
+            bad[2] = lwc.BatchDesc(5, 300, 64, 2, lwc.SIM_COSINE, lwc.PREC_FP32, lwc.MEM_DEVICE, 1)
+            launches0 = c.launch_count()
+            with pytest.raises(lwc.LwcError) as ei:
+                c.batch_list(bad, ptrs["E"], ptrs["V"], ptrs["w"], ptrs["conf"], ptrs["cw"], ptrs["agree"], ptrs["winner"], ptrs["rank"])()
+            assert ei.value.code == 400 and c.launch_count() == launches0
+            for bufs in keep:
+                for b in bufs.values():
+                    b.free()
+
+
+# ------------------------------------------------------------------ element types on the way in (SURVEY 8f3)
+
+@pytest.mark.parametrize("memory", ["host", "device"])
+@pytest.mark.parametrize("shape", [(700, 16, 1536, 4), (300, 32, 1000, 3), (40, 128, 512, 8), (33, 20, 50, 2), (5, 3, 7, 1)],
+                         ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+def test_f64_transport_gives_the_bits_of_host_conversion(ctx, lwc, oracle, shape, memory):
+    """Embedding.embedding is Vec<f64> (embeddings/response.rs:21).  LWC_ELEM_F64 sends the doubles and rounds on the
+    device; the result must be bit-identical to rounding on the host (lwc_stage_f64) and calling lwc_score_batch."""
+    R, N, D, M = shape
+    rng = np.random.default_rng(R + D)
+    E64 = rng.standard_normal((R, N, D)) * rng.lognormal(0, 0.5, (R, N, 1))
+    from lwc_b200 import synth
+
+    V, w = synth.votes(R, N, M, seed=R), synth.weights(R, M, seed=R)
+    E32 = np.empty((R, N, D), np.float32)
+    ctx.stage_f64(E64, E32)
+    assert np.array_equal(E32, E64.astype(np.float32))
+    want = ctx.score_batch(E32, V, w)
+    got = ctx.score_batch_typed(E64, lwc.ELEM_F64, V, w, memory=lwc.MEM_HOST if memory == "host" else lwc.MEM_DEVICE)
+    for k in want:
+        assert np.array_equal(got[k], want[k], equal_nan=True), k
+    ref = oracle.score_f64(E32, V, w, oracle.SIM_COSINE)
+    assert compare(got, ref, V) == 1.0
+
+
+BF16_TOL = 1e-2  # stated tolerance of the bf16 transport: 1e-2 of a request's top confidence
+
+
+@pytest.mark.parametrize("memory", ["host", "device"])
+@pytest.mark.parametrize("shape", [(700, 16, 1536, 4), (300, 32, 3072, 4), (200, 128, 1024, 16), (33, 20, 50, 2)],
+                         ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+def test_bf16_transport_within_its_stated_tolerance(ctx, lwc, oracle, shape, memory):
+    """LWC_ELEM_BF16: 2 bytes per element cross PCIe.  (a) The device side is exact: it must reproduce, within the
+    fp32 bar, the oracle run on the bf16-rounded embeddings.  (b) Against the oracle on the ORIGINAL embeddings the
+    stated 1e-2-of-top tolerance must hold and the winner must agree wherever the margin exceeds it."""
+    from lwc_b200 import synth
+
+    R, N, D, M = shape
+    E, V, w, _ = synth.make_batch(R, N, D, M, seed=40 + N, edge_cases=False)
+    bits = ctx.stage_f64_bf16(E.astype(np.float64))
+    # independent rounding model: nearest even on the upper 16 bits
+    u = E.view(np.uint32).astype(np.uint64)
+    model = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
+    assert np.array_equal(bits, model)
+    got = ctx.score_batch_typed(bits, lwc.ELEM_BF16, V, w, memory=lwc.MEM_HOST if memory == "host" else lwc.MEM_DEVICE)
+    E_rounded = (bits.astype(np.uint32) << 16).view(np.float32)
+    exact = oracle.score_f64(E_rounded, V, w, oracle.SIM_COSINE)
+    assert compare(got, exact, V) == 1.0                       # (a)
+    ref = oracle.score_f64(E, V, w, oracle.SIM_COSINE)         # (b)
+    top = np.abs(ref["conf"]).max(axis=1, keepdims=True)
+    assert np.all(np.abs(got["conf"] - ref["conf"]) <= BF16_TOL * top)
+    srt = np.sort(ref["conf"], axis=1)[:, ::-1]
+    clear = (ref["winner"] >= 0) & (srt[:, 0] - srt[:, 1] > 2 * BF16_TOL * top[:, 0])
+    assert np.array_equal(got["winner"][clear], ref["winner"][clear])
+    print(f"bf16 transport {shape}: max conf err / top = {float(np.max(np.abs(got['conf'] - ref['conf']) / np.maximum(top, 1e-30))):.2e}, "
+          f"winner agreement {float(np.mean(got['winner'] == ref['winner'])):.4f}")
+
+
+def test_typed_entry_argument_errors(ctx, lwc):
+    import ctypes
+
+    d = lwc.BatchDesc(1, 4, 8, 1, lwc.SIM_COSINE, lwc.PREC_FP32, lwc.MEM_HOST, 1)
+    one = ctypes.c_void_p(16)
+    rc = ctx.lib.lwc_score_batch_typed(ctx.handle, ctypes.byref(d), 7, one, one, one, None, None, None, None, None, None)
+    assert rc == 400 and "element type" in ctx.lib.lwc_last_error_message(ctx.handle).decode()
+    rc = ctx.lib.lwc_score_batch_typed(ctx.handle, ctypes.byref(d), lwc.ELEM_F64, ctypes.c_void_p(8), one, one, None, None, None, None,
+                                       None, None)
+    assert rc == 400 and "16-byte aligned" in ctx.lib.lwc_last_error_message(ctx.handle).decode()
+
+
+# ------------------------------------------------------------------ fp16-piece tcgen05 route: range check + fix-up pass
+
+def test_fp16_piece_route_fixes_up_requests_outside_fp16_range(ctx, lwc, oracle):
+    """The default fp32-grade route for 32 < N <= 128 splits every element into two fp16 pieces.  fp16 has 5
+    exponent bits, so the kernel marks requests whose candidates' norms it cannot represent exactly enough (tiny,
+    huge, zero, non-finite squared norm) and a second pass re-scores exactly those on tf32 pieces.  Here marked and
+    unmarked requests are interleaved inside every CTA's range; all of them must meet the fp32 bar."""
+    R, N, D, M = 640, 128, 1024, 8
+    E, V, w = fast_batch(R, N, D, M, seed=77)
+    scale = np.ones((R, 1, 1), np.float32)
+    scale[3::7] = 1e-6       # every candidate tiny: h would be subnormal or zero
+    scale[4::7] = 3e4        # elements far beyond 65504
+    scale[5::7] = 1e-3       # norms just under the kernel's threshold
+    E *= scale
+    E[6::7, 10] *= np.float32(1e-7)   # ONE tiny candidate among ordinary ones
+    E[9::14, 20, 5] = 7e4             # ONE out-of-range element
+    got = ctx.score_batch_device(E, V, w)
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    assert compare(got, want, V) == 1.0
+    properties_hold(got, V)
+    # position independence holds across the two passes too
+    perm = np.random.default_rng(5).permutation(R)[:300]
+    again = ctx.score_batch_device(E[perm], V[perm], w[perm])
+    for k in got:
+        assert np.array_equal(again[k], got[k][perm], equal_nan=True), k
+
+
+@pytest.mark.parametrize("shape", [(600, 128, 3072, 16), (600, 100, 2304, 16), (300, 40, 96, 3)], ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+def test_tf32_piece_route_remains_selectable(lwc, oracle, shape):
+    """LWC_TC_X3=tf32: the fp32-grade route on tf32 pieces alone (round 1's kernel, now also the fix-up pass)."""
+    from lwc_b200 import synth
+
+    R, N, D, M = shape
+    E, V, w, _ = synth.make_batch(R, N, D, M, seed=123 + N)
+    old = os.environ.get("LWC_TC_X3")
+    try:
+        os.environ["LWC_TC_X3"] = "tf32"
+        with lwc.Context(device=0) as c:
+            assert c.kernel_for(R, N, D, M) == "tc128_tf32x3"
+            got = c.score_batch_device(E, V, w)
+    finally:
+        if old is None:
+            os.environ.pop("LWC_TC_X3", None)
+        else:
+            os.environ["LWC_TC_X3"] = old
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    assert compare(got, want, V) == 1.0
+
+
+def test_small_pool_fp16_pieces_fall_back_outside_fp16_range(lwc, oracle):
+    """The one-CTA-per-request fp32-grade kernel (the cfg3 route) runs on fp16 pieces and re-scores a request on tf32
+    pieces when a candidate's squared norm shows that fp16's exponent range was left.  Ordinary, tiny, huge and
+    mixed requests interleaved; LWC_SMALL_X3=tf32 (tf32 pieces only) must give results within the same bar."""
+    R, N, D, M = 900, 32, 1536, 4
+    E, V, w = fast_batch(R, N, D, M, seed=61)
+    scale = np.ones((R, 1, 1), np.float32)
+    scale[2::5] = 1e-6
+    scale[3::5] = 5e4
+    E *= scale
+    E[4::10, 7] *= np.float32(1e-8)   # one tiny candidate among ordinary ones
+    E[9::10, 3, 100] = 1e5            # one out-of-range element
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    for env in (None, "tf32"):
+        old = os.environ.pop("LWC_SMALL_X3", None)
+        try:
+            if env:
+                os.environ["LWC_SMALL_X3"] = env
+            with lwc.Context(device=0) as c:
+                assert c.kernel_for(R, N, D, M) == ("small32_tf32x3" if env else "small32_f16x2")
+                got = c.score_batch_device(E, V, w)
+        finally:
+            os.environ.pop("LWC_SMALL_X3", None)
+            if old is not None:
+                os.environ["LWC_SMALL_X3"] = old
+        assert compare(got, want, V) == 1.0, env
+        properties_hold(got, V)
