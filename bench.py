@@ -367,6 +367,17 @@ def run_b200(args):
                               [d_out["rank"].data_ptr()] * k, stream=stream.cuda_stream)
 
     run_warm, run_timed, run_one = batch_list(args.warmup), batch_list(args.steps), batch_list(1)
+    if args.launch == "loop":  # A/B: one lwc_score_batch call per step from this interpreter (round 1's timed loop)
+        import ctypes
+        _vp, _fn = ctypes.c_void_p, ctx.lib.lwc_score_batch
+        _argv = [(ctx.handle, ctypes.byref(desc_dev), _vp(dE[j].data_ptr()), _vp(dV.data_ptr()), _vp(dw.data_ptr()),
+                  _vp(d_out["conf"].data_ptr()), _vp(d_out["cw"].data_ptr()), _vp(d_out["agree"].data_ptr()),
+                  _vp(d_out["winner"].data_ptr()), _vp(d_out["rank"].data_ptr()), _vp(stream.cuda_stream)) for j in range(n_rot)]
+
+        def run_timed():
+            for i in range(args.steps):
+                if _fn(*_argv[i % n_rot]):
+                    raise lwc_b200.LwcError(500, ctx.lib.lwc_last_error_message(ctx.handle).decode())
 
     def step_host():
         ctx.score_raw(desc_host, hE.ptr, hV.ptr, hw.ptr, out_host["conf"].ptr, out_host["cw"].ptr,
@@ -439,6 +450,38 @@ def run_b200(args):
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
+    # ---- the same call with the embeddings crossing PCIe as f64 (the reference's element type, rounded on the device)
+    # and as bf16 (opt-in transport, 1e-2 tolerance): what the element type on the wire costs / buys end to end
+    transports = {}
+    if world == 1 and not args.no_extras:
+        import ctypes
+
+        for name, et, dt in (("f64", lwc_b200.ELEM_F64, np.float64), ("bf16", lwc_b200.ELEM_BF16, np.uint16)):
+            hT = lwc_b200.HostBuffer(ctx, (R, N, D), dt)
+            if et == lwc_b200.ELEM_F64:
+                hT.array[...] = hE.array
+            else:
+                hT.array[...] = ctx.stage_f64_bf16(hE.array.astype(np.float64))
+            argv = (ctx.handle, ctypes.byref(desc_host), et, ctypes.c_void_p(hT.ptr), ctypes.c_void_p(hV.ptr), ctypes.c_void_p(hw.ptr),
+                    *[ctypes.c_void_p(out_host[k].ptr) for k in ("conf", "cw", "agree", "winner", "rank")], None)
+            for _ in range(2):
+                ctx._check(ctx.lib.lwc_score_batch_typed(*argv))
+            t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t1[0].record(ext)
+            for _ in range(e2e_steps):
+                ctx._check(ctx.lib.lwc_score_batch_typed(*argv))
+            t1[1].record(ext)
+            torch.cuda.synchronize()
+            ms = t1[0].elapsed_time(t1[1]) / e2e_steps
+            transports[name] = {"value": R / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms,
+                                "h2d_bytes_per_step": hT.nbytes + hV.nbytes + hw.nbytes}
+            transports[name]["winners"] = out_host["winner"].array.copy()
+            hT.free()
+        step_host()  # leave the fp32 transport's results in the host buffers for the checks below
+        for name in transports:
+            wn = transports[name].pop("winners")
+            transports[name]["winner_agreement_with_fp32_transport"] = float(np.mean(wn == out_host["winner"].array))
+
     # the two paths must agree bit for bit on the same batch (device batch 0 == host batch)
     run_one()
     torch.cuda.synchronize()
@@ -470,7 +513,8 @@ def run_b200(args):
                 "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "wall_ms_per_step": wall_ms / e2e_steps,
                 "api": "lwc_score_batch(LWC_MEM_HOST), pinned host buffers",
                 "achieved_gbs": e2e_gbs, "h2d_peak_gbs": pcie, "frac_of_h2d_peak": e2e_gbs / pcie,
-                "bound": "PCIe: plain pinned cudaMemcpyAsync H2D of the same bytes on this box = h2d_peak_gbs"},
+                "bound": "PCIe: plain pinned cudaMemcpyAsync H2D of the same bytes on this box = h2d_peak_gbs",
+                "other_transports": transports or None},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": load_traffic(kernel, R), "kernel": kernel, "peak_source": peak_src,
@@ -503,23 +547,46 @@ def run_b200(args):
     return 0
 
 
-def host_types_leg(device):
-    """End to end FROM THE REFERENCE'S OWN TYPES: tools/e2e_host (C++) builds cfg2 as per-request
+def host_types_leg(device, with_cpu=True):
+    """End to end FROM THE REFERENCE'S OWN TYPES: tools/e2e_host (C++) builds each shape as per-request
     CreateEmbeddingResponse-shaped rows of Vec<f64> plus Option<Vec<f64>> votes, submits them to lwc::Batcher from
-    several host threads and collects Tally futures; wall clock.  Returns the tool's JSON (or why it did not run)."""
+    several host threads and collects Tally futures; wall clock.  cfg2's shape is the headline; cfg3's and cfg4's
+    shapes show how the ratio to the CPU port moves with the pool size (the CPU's Gram cost grows with N^2, the bytes
+    the host has to convert and ship with N).  Returns the tool's JSON per shape (or why it did not run)."""
     import subprocess
 
     exe = os.path.join(ROOT, "tools", "e2e_host")
     if not os.path.exists(exe):
         return {"unavailable": "tools/e2e_host is not built (python __graft_entry__.py)"}
-    try:
-        out = subprocess.run([exe, "--device", str(device)], capture_output=True, text=True, timeout=300)
-        lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
-        if out.returncode != 0 or not lines:
-            return {"unavailable": f"tools/e2e_host exited {out.returncode}: {out.stderr[-300:]}"}
-        return json.loads(lines[-1])
-    except Exception as exc:  # a side leg must never cost the bench line
-        return {"unavailable": repr(exc)}
+    out = {}
+    shapes = (("cfg2_shape", 4096, 16, 1536, 4, 5), ("cfg3_shape", 1024, 32, 3072, 4, 4), ("cfg4_shape", 256, 128, 3072, 16, 4))
+    for name, R, N, D, M, rounds in shapes:
+        try:
+            run = subprocess.run([exe, "--device", str(device), "--requests", str(R), "--n", str(N), "--d", str(D), "--m", str(M),
+                                  "--rounds", str(rounds), "--batch", str(max(32, min(512, R // 4)))],
+                                 capture_output=True, text=True, timeout=300)
+            lines = [l for l in run.stdout.splitlines() if l.startswith("{")]
+            if run.returncode != 0 or not lines:
+                out[name] = {"unavailable": f"tools/e2e_host exited {run.returncode}: {run.stderr[-300:]}"}
+                continue
+            out[name] = json.loads(lines[-1])
+            if with_cpu:
+                import oracle
+                from lwc_b200 import synth
+
+                n = min(R, 256 if N <= 32 else 64)
+                E, V, w, _ = synth.make_batch(n, N, D, M, seed=9, edge_cases=False)
+                cores = host_cores()
+                t, reps = 0.0, 0
+                while t < 3.0 and reps < 64:
+                    t += oracle.score_port(E, V, w, oracle.SIM_COSINE, nthreads=cores)["seconds"]
+                    reps += 1
+                out[name]["cpu_port_same_shape"] = {"value": n * reps / t, "unit": UNIT, "cores": cores,
+                                                    "sample": f"{reps} pass(es) over {n} requests (fp32 inputs already contiguous)"}
+                out[name]["ratio_to_cpu_port"] = out[name]["value"] / out[name]["cpu_port_same_shape"]["value"]
+        except Exception as exc:  # a side leg must never cost the bench line
+            out[name] = {"unavailable": repr(exc)}
+    return out
 
 
 def device_batch(torch, R, N, D, seed):
@@ -962,6 +1029,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e", action="store_true", help="side workloads cfg3/cfg4: add the host-buffer path and the CPU port")
+    ap.add_argument("--launch", default="list", choices=["list", "loop"], help="timed launches: one lwc_score_batches call (default) or a Python loop of lwc_score_batch calls")
     ap.add_argument("--no-extras", action="store_true", help="skip the cfg3 / cfg4 / cfg5 side records of the main line")
     ap.add_argument("--no-host-leg", action="store_true", help="skip tools/e2e_host (end to end from the reference's types)")
     ap.add_argument("--no-overlap", action="store_true", help="do not set LWC_CTX_INPUTS_RESIDENT (launches fully serialised)")

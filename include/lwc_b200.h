@@ -301,7 +301,9 @@ int32_t lwc_pool_p2p_attach(lwc_ctx *ctx, const void *all_handles /* nranks * 12
  *   memory = LWC_MEM_HOST: q, weights, top_idx, top_sim are host pointers and the call blocks.
  *   memory = LWC_MEM_DEVICE: they are device pointers and the call is asynchronous on the context's stream
  *   (lwc_ctx_stream): `weights` can be passed as `w` (w_per_request = 1) to an lwc_score_batch call on
- *   that stream without touching the host.  base / minw / maxw are host arrays either way. */
+ *   that stream without touching the host -- also under LWC_CTX_INPUTS_RESIDENT: the context remembers that a
+ *   producer of weights is queued and makes the next scoring launch wait for it before reading its inputs.
+ *   base / minw / maxw are host arrays either way. */
 int32_t lwc_table_load(lwc_ctx *ctx, const float *T, const float *Q, int64_t rows, int32_t D, int32_t M);
 int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32_t top, const float *base,
                           const float *minw, const float *maxw, float *weights, int32_t *top_idx, float *top_sim,

@@ -216,6 +216,8 @@ cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st, 
     return cudaGetLastError();
 }
 
+cudaError_t ensure_fix_flags(lwc_ctx *ctx, int R);
+
 // fp32-grade route at kind::f16 rate (score_tc16.cuh) + its fix-up pass: the requests whose norms fall outside
 // what fp16 pieces represent exactly enough are marked by the first kernel and re-scored by the tf32 kernel.
 cudaError_t launch_tc16(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
@@ -231,16 +233,9 @@ cudaError_t launch_tc16(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st
         if (e != cudaSuccess) return e;
         configured[ctx->device & 63] = true;
     }
-    if ((size_t)p.R * sizeof(int) > ctx->tc_flags_cap) { // one word per request: which requests need the fix-up pass
-        if (ctx->tc_flags) {
-            cudaError_t e = cudaFree(ctx->tc_flags);
-            if (e != cudaSuccess) return e;
-        }
-        ctx->tc_flags = nullptr, ctx->tc_flags_cap = 0;
-        const size_t want = (size_t)p.R * sizeof(int) * 2 + 256;
-        cudaError_t e = cudaMalloc(&ctx->tc_flags, want);
+    {
+        cudaError_t e = ensure_fix_flags(ctx, p.R);
         if (e != cudaSuccess) return e;
-        ctx->tc_flags_cap = want;
     }
     CUtensorMap tm;
     if (!make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, 2)) return cudaErrorInvalidValue;
@@ -250,6 +245,20 @@ cudaError_t launch_tc16(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st
     if (e != cudaSuccess) return e;
     ctx->launches++;
     return launch_tc<true>(ctx, p, st, static_cast<const int *>(ctx->tc_flags));
+}
+
+// per-request fix-up marks of the fp16-piece tcgen05 route (score_tc16.cuh): one word per request
+cudaError_t ensure_fix_flags(lwc_ctx *ctx, int R) {
+    if ((size_t)R * sizeof(int) <= ctx->tc_flags_cap) return cudaSuccess;
+    if (ctx->tc_flags) {
+        cudaError_t e = cudaFree(ctx->tc_flags);
+        if (e != cudaSuccess) return e;
+    }
+    ctx->tc_flags = nullptr, ctx->tc_flags_cap = 0;
+    const size_t want = (size_t)R * sizeof(int) * 2 + 256;
+    cudaError_t e = cudaMalloc(&ctx->tc_flags, want);
+    if (e == cudaSuccess) ctx->tc_flags_cap = want;
+    return e;
 }
 
 template <int NT, bool X3, int NCW, int NF>
@@ -308,25 +317,46 @@ cudaError_t launch_stream(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t 
     }
 }
 
+// Small pools (N <= 32): which kernel, on which pieces.
+//   ring kernel (score_stream): tf32 pieces.  16-row pools run it at 0.97 of HBM.  An fp16-piece form with a fix-up pass
+//   was built and measured for 32-row pools (cfg3 slice 1.231 ms against 1.127 ms for the direct kernel below: its eight
+//   consumer warps became issue-bound on the piece arithmetic) and dropped.
+//   direct kernel (score_small): fp32-grade 32-row pools by default, and everything under LWC_SMALL_IMPL=direct;
+//   fp16 pieces with an inline tf32 fallback (LWC_SMALL_X3=tf32: tf32 pieces only).
+struct SmallRoute {
+    bool stream; // persistent ring kernel, else one CTA per request
+    bool f16;    // fp32-grade Gram on fp16 pieces
+};
+SmallRoute small_route(const lwc_ctx *ctx, const Plan &pl) {
+    const bool f16_ok = pl.x3 && !ctx->small_x3_tf32;
+    SmallRoute r;
+    if (ctx->small_impl == 1)
+        r.stream = false;
+    else if (ctx->force_stream)
+        r.stream = true;
+    else
+        r.stream = !(pl.np == 32 && pl.x3); // 32-row fp32-grade pools: the direct kernel is faster on either kind of pieces
+    r.f16 = f16_ok && !r.stream;
+    return r;
+}
+
 int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStream_t st) {
     if (p.R == 0) return LWC_OK;
     cudaError_t e = cudaSuccess;
-    // 32-candidate pools with the compensated 3xTF32 Gram are bound by the legacy mma.sync pipe, not by
-    // HBM; there the one-CTA-per-request kernel (more warps in flight) measured 83 % vs 80 % of HBM peak.
-    const bool stream_route = ctx->small_impl == 0 && !(pl.np == 32 && pl.x3 && !ctx->force_stream);
+    const SmallRoute sr = small_route(ctx, pl);
     if (pl.route == ROUTE_TC) {
         e = !pl.x3 ? launch_tc<false>(ctx, p, st) : (ctx->tc_x3_tf32 ? launch_tc<true>(ctx, p, st) : launch_tc16(ctx, p, st));
-    } else if (pl.route == ROUTE_SMALL && stream_route) {
+    } else if (pl.route == ROUTE_SMALL && sr.stream) {
         if (pl.np == 16)
             e = pl.x3 ? launch_stream<16, true>(ctx, p, st) : launch_stream<16, false>(ctx, p, st);
         else
             e = pl.x3 ? launch_stream<32, true>(ctx, p, st) : launch_stream<32, false>(ctx, p, st);
     } else if (pl.route == ROUTE_SMALL) {
         if (pl.np == 16)
-            e = pl.x3 ? launch_small<16, true>(p, st, ctx->small_kw, ctx->small_u, !ctx->small_x3_tf32)
+            e = pl.x3 ? launch_small<16, true>(p, st, ctx->small_kw, ctx->small_u, sr.f16)
                       : launch_small<16, false>(p, st, ctx->small_kw, ctx->small_u, false);
         else // 32-row pools: 2 warps per request measured best (1.157 vs 1.185 ms at KW=4, cfg3 slice)
-            e = pl.x3 ? launch_small<32, true>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u, !ctx->small_x3_tf32)
+            e = pl.x3 ? launch_small<32, true>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u, sr.f16)
                       : launch_small<32, false>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u, false);
     } else {
         if (pl.np == 32)
@@ -631,10 +661,9 @@ const char *lwc_kernel_for(const lwc_ctx *ctx, const lwc_batch_desc *desc) {
     // alignment is unknown here: assume the documented 16-byte alignment of E
     const Plan pl = plan_for(*desc, nullptr);
     if (ctx && ctx->tc_x3_tf32 && pl.route == ROUTE_TC && pl.x3) return "tc128_tf32x3";
-    if (ctx && pl.route == ROUTE_SMALL && pl.x3 && !ctx->small_x3_tf32) {
-        // the one-CTA-per-request kernel runs the fp32-grade Gram on fp16 pieces; the persistent ring kernel on tf32 pieces
-        const bool stream_route = ctx->small_impl == 0 && !(pl.np == 32 && !ctx->force_stream);
-        if (!stream_route) return pl.np == 16 ? "small16_f16x2" : "small32_f16x2";
+    if (ctx && pl.route == ROUTE_SMALL && pl.x3) {
+        const SmallRoute sr = small_route(ctx, pl);
+        if (sr.f16) return pl.np == 16 ? "small16_f16x2" : "small32_f16x2";
     }
     return pl.name;
 }
@@ -677,6 +706,10 @@ static int32_t score_typed(lwc_ctx *ctx, const char *fn, const lwc_batch_desc *d
     p.w_per_request = d.w_per_request;
     p.cosine = cosine ? 1 : 0;
     p.inputs_resident = (ctx->flags & LWC_CTX_INPUTS_RESIDENT) ? 1 : 0;
+    if (ctx->weights_in_flight) { // lwc_table_weights(LWC_MEM_DEVICE) queued a producer of `w` on the context's stream:
+        p.inputs_resident = 0;    // this launch must wait for it before it reads anything
+        ctx->weights_in_flight = 0;
+    }
     if (typed && cosine) {
         // device-resident f64 / bf16: converted into the context's conversion buffer on the same stream
         const size_t n = (size_t)d.R * d.N * d.D;
@@ -738,6 +771,10 @@ int32_t lwc_score_batches(lwc_ctx *ctx, int32_t n_batches, const lwc_batch_desc 
         p.w_per_request = d.w_per_request;
         p.cosine = d.similarity == LWC_SIM_COSINE ? 1 : 0;
         p.inputs_resident = (ctx->flags & LWC_CTX_INPUTS_RESIDENT) ? 1 : 0;
+        if (ctx->weights_in_flight) { // see score_typed
+            p.inputs_resident = 0;
+            ctx->weights_in_flight = 0;
+        }
         const int rc = launch_plan(ctx, pl, p, st);
         if (rc) return rc;
     }
@@ -798,7 +835,22 @@ int32_t lwc_vote_from_logprobs(lwc_ctx *ctx, int32_t n_rows, int32_t n_top, int3
     const bool vec4 = n_top >= 4 && n_top % 4 == 0 && tile4 <= 48 * 1024 &&
                       ((reinterpret_cast<uintptr_t>(dlp) | reinterpret_cast<uintptr_t>(dlf)) & 15u) == 0;
     const unsigned tiles = (unsigned)((n_rows + lwc::kVoteRows - 1) / lwc::kVoteRows);
-    if (vec4) {
+    const size_t ring = lwc::vote_ring_smem(n_top, n_choices);
+    static const bool no_ring = getenv("LWC_VOTE_IMPL") && !strcmp(getenv("LWC_VOTE_IMPL"), "tile"); // A/B knob
+    if (vec4 && !no_ring && ring <= (size_t)ctx->max_smem_optin && tiles >= 2u * (unsigned)ctx->sm_count) {
+        // many tiles: the persistent ring kernel (inputs by bulk async copies, several tiles in flight per CTA)
+        static std::atomic<bool> configured[64];
+        if (!configured[ctx->device & 63]) {
+            CUDA_TRY(ctx, cudaFuncSetAttribute(lwc::vote_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin));
+            configured[ctx->device & 63] = true;
+        }
+        int per_sm = (int)((size_t)ctx->max_smem_optin / (ring + 1024));
+        if (per_sm < 1) per_sm = 1;
+        if (per_sm > 4) per_sm = 4;
+        unsigned grid = (unsigned)(ctx->sm_count * per_sm);
+        if (grid > tiles) grid = tiles;
+        lwc::vote_ring_kernel<<<grid, lwc::kVoteRows, ring, st>>>(dlp, dlf, dV, n_rows, n_top, n_choices);
+    } else if (vec4) {
         lwc::vote_tile4_kernel<<<tiles, lwc::kVoteRows, tile4, st>>>(dlp, dlf, dV, n_rows, n_top, n_choices,
                                                                     lwc::vote_tile4_pitch4(n_top));
     } else if (tile <= 48 * 1024) {

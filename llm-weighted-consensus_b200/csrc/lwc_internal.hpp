@@ -63,6 +63,8 @@ struct lwc_ctx {
     size_t table_cap[5] = {0};
     long long table_rows = 0;
     int table_D = 0, table_M = 0;
+    int weights_in_flight = 0; // lwc_table_weights(LWC_MEM_DEVICE) has queued a kernel that writes a caller's `w`: the next
+                               // lwc_score_batch must not let its input reads run ahead of the stream (LWC_CTX_INPUTS_RESIDENT)
     void *typed_buf = nullptr; // fp32 copy of device-resident f64 / bf16 embeddings (lwc_score_batch_typed)
     size_t typed_cap = 0;
     void *tc_flags = nullptr;  // per-request fix-up marks of the fp16-piece tcgen05 route (score_tc16.cuh)

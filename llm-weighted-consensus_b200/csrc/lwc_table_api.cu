@@ -211,6 +211,7 @@ int32_t lwc_table_weights(lwc_ctx *ctx, const float *q, int32_t n_prompts, int32
         }
     }
     if (!dev) CUDA_TRY(ctx, cudaStreamSynchronize(st)); // host results are valid on return; device results in stream order
+    if (dev) ctx->weights_in_flight = 1; // see lwc_score_batch: the next launch keeps full stream order
     return LWC_OK;
 }
 

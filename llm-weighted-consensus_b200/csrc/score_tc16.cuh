@@ -33,7 +33,11 @@
 //                      the request, S_ij = X_ij + 2^-11 (Y_ij + Y_ji) via the row / warp-transpose fold.
 // Shared-memory traffic per unit: 32 KB TMA in, 32 + 32 KB transform, 16 + 32 KB operand reads = 144 KB against
 // the 192 KB per 64 columns of the tf32 scheme; tensor time 4 x 187 clk against ~1,480 clk a unit has at HBM speed.
-// Bound: HBM.
+// Measured (cfg4, 8,192 requests): 2.61 ms against 3.03 ms on tf32 pieces and 1.91 ms for the single-pass TF32 route on
+// the same box -- 0.77 of HBM.  Bound: the SHARED-MEMORY pipe (ncu, profiles/r2_tc16_raw.csv: LSU wavefronts 50 % +
+// tensor operand reads 24 % + TMA writes; tensor pipe 33 %, DRAM 5.0 TB/s): 144 KB of shared-memory traffic per 32 KB of
+// HBM traffic.  Tried and dropped: asking L2 for the units eight ahead of the ring (cp.async.bulk.prefetch.tensor) so
+// that HBM latency stops depending on ring depth -- 2.80 ms, i.e. latency was not the limit.
 #pragma once
 
 #include <cuda_fp16.h>
@@ -46,10 +50,6 @@ constexpr int kT16Threads = 320;
 constexpr int kT16UnitBytes = 2 * kTcSlabBytes; // 64 columns: two fp32 slabs in, [h ; l] fp16 tiles out
 constexpr int kT16ChunkUnits = 4;               // 16 MMAs (256 columns) per in-TMEM accumulation chain of X
 constexpr int kT16MaxStages = 6;
-#ifndef LWC_T16_PREFETCH
-#define LWC_T16_PREFETCH 8
-#endif
-constexpr int kT16Prefetch = LWC_T16_PREFETCH; // units (32 KB) requested from L2 ahead of the shared-memory ring
 constexpr float kT16LoScale = 1.0f / 2048.0f;   // Y carries 2^11
 constexpr float kT16MinNorm2 = 1.0f / 4096.0f;  // squared norm below which fp16 pieces may have lost bits
 
@@ -64,11 +64,6 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint6
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc)
         : "memory");
-}
-
-__device__ __forceinline__ void tma_prefetch_4d(const CUtensorMap *tm, int c0, int c1, int c2, int c3) {
-    asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];" ::"l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-                 : "memory");
 }
 
 // 8 fp32 values -> 8 fp16 h (one 16-byte chunk) and 8 fp16 l
@@ -155,22 +150,8 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
             const uint32_t ring_u32 = smem_u32(ring);
             int slot = 0;
             uint32_t phase = 0;
-            // A stage stays occupied from the TMA issue until its MMAs have read it (in-place transform), so the ring
-            // alone cannot keep the ~90 KB per SM in flight that HBM latency needs.  The producer therefore asks L2 for
-            // the units kT16Prefetch ahead of the one it loads: the later TMA load is an L2 hit, and the bytes in
-            // flight from HBM no longer depend on shared memory (148 SMs x 8 units x 32 KB = 38 MB of the 126 MB L2).
-            const int total = nreq * upr;
-            int pq = 0, pu = 0; // request / unit of the next prefetch
-            for (int k = 0; k < min(kT16Prefetch, total); ++k) {
-                tma_prefetch_4d(&tmE, 0, 0, 2 * pu, r_begin + pq);
-                if (++pu == upr) pu = 0, ++pq;
-            }
             for (int q = 0; q < nreq; ++q)
                 for (int u = 0; u < upr; ++u) {
-                    if (pq < nreq) {
-                        tma_prefetch_4d(&tmE, 0, 0, 2 * pu, r_begin + pq);
-                        if (++pu == upr) pu = 0, ++pq;
-                    }
                     mbar_wait_backoff(empty0 + 8 * slot, phase ^ 1u, 40);
                     mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)kT16UnitBytes); // OOB zero-fill counts too
                     tma_load_4d(ring_u32 + slot * kT16UnitBytes, &tmE, 0, 0, 2 * u, r_begin + q, full0 + 8 * slot);

@@ -13,7 +13,7 @@
 // vote_from_logprobs_kernel (one warp per row) remains for shapes whose tile does not fit 48 KB.
 #pragma once
 
-#include "score_common.cuh"
+#include "score_stream.cuh" // mbarrier / bulk-copy helpers
 
 namespace lwc {
 
@@ -231,6 +231,107 @@ inline int vote_tile4_pitch4(int n_top) { // 16-byte pieces per staged row: odd,
 }
 inline size_t vote_tile4_smem(int n_top, int n_choices) {
     return (size_t)kVoteRows * vote_tile4_pitch4(n_top) * 32 + (size_t)kVoteRows * (size_t)(n_choices + 1) * 4;
+}
+
+// vote_ring_kernel: persistent form of vote_tile4_kernel.  Round 2's ncu capture of the tile kernel showed neither
+// DRAM (65 %) nor the LSU pipe (71 %) saturated: every CTA ran load -> compute -> store phases in sequence, and the
+// 7 CTAs an SM holds overlapped them only by chance.  Here a CTA keeps a ring of kVoteRingStages input tiles in
+// flight: a tile's (logprob, leaf) rows are two CONTIGUOUS blocks of global memory (128 rows x n_top x 4 B), so one
+// thread fetches each with a single bulk async copy (cp.async.bulk, completion on the stage's mbarrier) -- no
+// staging instructions, no LSU wavefronts, and the loads of tile k+2 are in flight while tile k is computed.  The
+// compute phase is vote_tile4_kernel's: thread = row, 128-bit shared reads of its own row (pitch n_top words,
+// conflict-free when n_top / 4 is odd, two-way otherwise), branch-free alternatives, output tile [j][128].
+constexpr int kVoteRingStages = 3;
+
+inline size_t vote_ring_smem(int n_top, int n_choices) {
+    return (size_t)kVoteRingStages * kVoteRows * (size_t)n_top * 8 + (size_t)kVoteRows * (size_t)(n_choices + 1) * 4 + 64;
+}
+
+__global__ void __launch_bounds__(kVoteRows) vote_ring_kernel(const float *__restrict__ logprob, const int32_t *__restrict__ leaf,
+                                                              float *__restrict__ V, int n_rows, int n_top, int n_choices) {
+    extern __shared__ __align__(128) unsigned char vring[];
+    const int tile_words = kVoteRows * n_top;                                   // words per array and stage
+    float *lp_s = reinterpret_cast<float *>(vring);                              // [stages][128][n_top]
+    int32_t *lf_s = reinterpret_cast<int32_t *>(lp_s + (size_t)kVoteRingStages * tile_words);
+    float *out_s = reinterpret_cast<float *>(lf_s + (size_t)kVoteRingStages * tile_words); // [n_choices + 1][128]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(out_s + (size_t)kVoteRows * (n_choices + 1));
+    const uint32_t full0 = smem_u32(bars);
+    const int tid = threadIdx.x;
+    const int ntiles = (n_rows + kVoteRows - 1) / kVoteRows;
+    const int q4 = n_top >> 2;
+
+    if (tid == 0) {
+        for (int s = 0; s < kVoteRingStages; ++s) mbar_init(full0 + 8 * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](int tile, int stage) { // thread 0: both arrays of one tile, two bulk copies
+        const long long row0 = (long long)tile * kVoteRows;
+        const int rows = (int)(n_rows - row0 < kVoteRows ? n_rows - row0 : kVoteRows);
+        const uint32_t bytes = (uint32_t)rows * (uint32_t)n_top * 4u;
+        mbar_arrive_expect_tx(full0 + 8 * stage, 2 * bytes);
+        bulk_g2s(smem_u32(lp_s + (size_t)stage * tile_words), logprob + (size_t)row0 * n_top, bytes, full0 + 8 * stage);
+        bulk_g2s(smem_u32(lf_s + (size_t)stage * tile_words), leaf + (size_t)row0 * n_top, bytes, full0 + 8 * stage);
+    };
+    if (tid == 0)
+        for (int k = 0; k < kVoteRingStages; ++k) {
+            const int tile = blockIdx.x + k * gridDim.x;
+            if (tile < ntiles) issue(tile, k);
+        }
+    int stage = 0;
+    uint32_t phase = 0;
+    const unsigned nc = (unsigned)n_choices;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long row0 = (long long)tile * kVoteRows;
+        const int rows = (int)(n_rows - row0 < kVoteRows ? n_rows - row0 : kVoteRows);
+        for (int j = 0; j <= n_choices; ++j) out_s[j * kVoteRows + tid] = 0.f; // own column only: no barrier needed
+        mbar_wait(full0 + 8 * stage, phase);
+        if (tid < rows) {
+            const float4 *x4 = reinterpret_cast<const float4 *>(lp_s + (size_t)stage * tile_words + (size_t)tid * n_top);
+            const int4 *l4 = reinterpret_cast<const int4 *>(lf_s + (size_t)stage * tile_words + (size_t)tid * n_top);
+            float s = 0.f;
+#pragma unroll 5
+            for (int k = 0; k < q4; ++k) {
+                const float4 x = x4[k];
+                const int4 l = l4[k];
+                const float xs[4] = {x.x, x.y, x.z, x.w};
+                const int ls[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const bool ok = (unsigned)ls[e] < nc && xs[e] == xs[e];
+                    const float pk = ok ? exp_logprob(xs[e]) : 0.f;
+                    const int j = ok ? ls[e] : n_choices; // spare column
+                    out_s[j * kVoteRows + tid] += pk;     // client.rs:1765-1784, in alternative order
+                    s += pk;
+                }
+            }
+            const bool ok = s > 0.f; // else unreachable!() in the reference (client.rs:1786-1788): mark the voter absent
+            const float inv = ok ? 1.0f / s : 0.f;
+            const float nanv = __int_as_float(0x7fc00000);
+            float *out = V + (size_t)(row0 + tid) * n_choices;
+            if ((n_choices & 3) == 0 && (reinterpret_cast<uintptr_t>(V) & 15u) == 0) {
+                for (int j = 0; j < n_choices; j += 4) {
+                    float4 r4;
+                    r4.x = ok ? out_s[j * kVoteRows + tid] * inv : nanv;
+                    r4.y = ok ? out_s[(j + 1) * kVoteRows + tid] * inv : nanv;
+                    r4.z = ok ? out_s[(j + 2) * kVoteRows + tid] * inv : nanv;
+                    r4.w = ok ? out_s[(j + 3) * kVoteRows + tid] * inv : nanv;
+                    *reinterpret_cast<float4 *>(out + j) = r4;
+                }
+            } else {
+                for (int j = 0; j < n_choices; ++j) out[j] = ok ? out_s[j * kVoteRows + tid] * inv : nanv;
+            }
+        }
+        __syncthreads(); // every thread has read the stage: it may be refilled
+        if (tid == 0) {
+            const int next = tile + kVoteRingStages * gridDim.x;
+            if (next < ntiles) issue(next, stage);
+        }
+        if (++stage == kVoteRingStages) {
+            stage = 0;
+            phase ^= 1u;
+        }
+    }
 }
 
 } // namespace lwc
