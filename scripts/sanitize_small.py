@@ -1,4 +1,4 @@
-"""One small invocation of every kernel, for `compute-sanitizer --tool memcheck|racecheck python tests/sanitize_small.py`
+"""One small invocation of every kernel, for `compute-sanitizer --tool memcheck|racecheck python scripts/sanitize_small.py`
 (one tool per gpurun call).  Prints SANITIZE_RUN_OK when every call returned and matched the oracle loosely."""
 import os
 import sys
