@@ -526,7 +526,7 @@ def run_b200(args):
 
         sl = slice(0, 256)
         line["parity_sample"] = parity_sample(oracle, hE.array[sl], V[sl], w[sl], {k: v[sl] for k, v in dev_np.items()})
-    if world == 1:
+    if world == 1 and not args.no_cfg1:
         line["gpu_cfg1"] = cfg1_gpu(ctx, lwc_b200, synth)
     if not args.no_extras:
         line["extra"] = run_extras(args, torch, lwc_b200, synth, ctx, dist, rank, world, local_rank)
@@ -1031,6 +1031,7 @@ def main():
     ap.add_argument("--e2e", action="store_true", help="side workloads cfg3/cfg4: add the host-buffer path and the CPU port")
     ap.add_argument("--launch", default="list", choices=["list", "loop"], help="timed launches: one lwc_score_batches call (default) or a Python loop of lwc_score_batch calls")
     ap.add_argument("--no-extras", action="store_true", help="skip the cfg3 / cfg4 / cfg5 side records of the main line")
+    ap.add_argument("--no-cfg1", action="store_true", help="skip the single-request latency leg (2,100 tiny launches; used for the ncu launch list)")
     ap.add_argument("--no-host-leg", action="store_true", help="skip tools/e2e_host (end to end from the reference's types)")
     ap.add_argument("--no-overlap", action="store_true", help="do not set LWC_CTX_INPUTS_RESIDENT (launches fully serialised)")
     ap.add_argument("--workload", default=WORKLOAD, choices=["cfg2", "cfg3", "cfg4", "cfg2x4", "pool", "table", "vote"],

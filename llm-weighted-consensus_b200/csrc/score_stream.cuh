@@ -114,6 +114,7 @@ struct StreamCfg {
     static constexpr size_t smem_bytes(int ks, int stages) { return fixed_bytes() + (size_t)stages * stage_bytes(ks); }
 };
 
+constexpr bool kStreamFlush = kMmaChain < (1 << 20); // A/B builds (-DLWC_MMA_CHAIN=1000000) compile the flush out
 constexpr int kVotePrefetch = 4; // voters whose rows a finaliser keeps in registers
 
 template <int NT, bool X3, int NCW, int NFIN>
@@ -265,7 +266,7 @@ score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
                     slot = 0;
                     phase ^= 1u;
                 }
-                if (X3 && ++since == flush_stages && s + 1 < spr) {
+                if (X3 && kStreamFlush && ++since == flush_stages && s + 1 < spr) {
                     since = 0;
 #pragma unroll
                     for (int a = 0; a < MT; ++a)
@@ -280,7 +281,7 @@ score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
                             }
                 }
             }
-            if (X3) {
+            if (X3 && kStreamFlush) {
 #pragma unroll
                 for (int a = 0; a < MT; ++a)
 #pragma unroll
