@@ -50,6 +50,18 @@ constexpr int kT16Threads = 320;
 constexpr int kT16UnitBytes = 2 * kTcSlabBytes; // 64 columns: two fp32 slabs in, [h ; l] fp16 tiles out
 constexpr int kT16ChunkUnits = 4;               // 16 MMAs (256 columns) per in-TMEM accumulation chain of X
 constexpr int kT16MaxStages = 6;
+// polling back-off (ns) of the producer / MMA issuer / transform warps: every poll is a shared-memory wavefront on the
+// pipe that bounds this kernel
+#ifndef LWC_T16_BO_P
+#define LWC_T16_BO_P 40
+#endif
+#ifndef LWC_T16_BO_M
+#define LWC_T16_BO_M 20
+#endif
+#ifndef LWC_T16_BO_T
+#define LWC_T16_BO_T 40
+#endif
+constexpr unsigned kT16BackoffP = LWC_T16_BO_P, kT16BackoffM = LWC_T16_BO_M, kT16BackoffT = LWC_T16_BO_T;
 constexpr float kT16LoScale = 1.0f / 2048.0f;   // Y carries 2^11
 constexpr float kT16MinNorm2 = 1.0f / 4096.0f;  // squared norm below which fp16 pieces may have lost bits
 
@@ -152,7 +164,7 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
             uint32_t phase = 0;
             for (int q = 0; q < nreq; ++q)
                 for (int u = 0; u < upr; ++u) {
-                    mbar_wait_backoff(empty0 + 8 * slot, phase ^ 1u, 40);
+                    mbar_wait_backoff(empty0 + 8 * slot, phase ^ 1u, kT16BackoffP);
                     mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)kT16UnitBytes); // OOB zero-fill counts too
                     tma_load_4d(ring_u32 + slot * kT16UnitBytes, &tmE, 0, 0, 2 * u, r_begin + q, full0 + 8 * slot);
                     if (++slot == S) {
@@ -186,7 +198,7 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
                         tc_fence_after();
                         d_tmem = tmem_base + ab * 256u;
                     }
-                    mbar_wait_backoff(ready0 + 8 * slot, phase, 20); // the stage holds [h ; l]
+                    mbar_wait_backoff(ready0 + 8 * slot, phase, kT16BackoffM); // the stage holds [h ; l]
                     tc_fence_after();
                     const uint32_t unit = ring_u32 + slot * kT16UnitBytes;
 #pragma unroll
@@ -218,20 +230,27 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
         uint32_t phase = 0;
         for (int q = 0; q < nreq; ++q)
             for (int u = 0; u < upr; ++u) {
-                mbar_wait_backoff(full0 + 8 * slot, phase, 40);
+                mbar_wait_backoff(full0 + 8 * slot, phase, kT16BackoffT);
                 const uint32_t base = smem_u32(ring) + (uint32_t)slot * kT16UnitBytes;
-#pragma unroll 2
-                for (int g = tw; g < 16; g += NTW) { // 8-row atoms of this warp
-                    const uint32_t a0 = base + (uint32_t)g * 1024u, a1 = a0 + (uint32_t)kTcSlabBytes;
-                    float4 x00, x01, x10, x11;
-                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x00.x), "=f"(x00.y), "=f"(x00.z), "=f"(x00.w) : "r"(a0 + in0));
-                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x01.x), "=f"(x01.y), "=f"(x01.z), "=f"(x01.w) : "r"(a0 + in1));
-                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x10.x), "=f"(x10.y), "=f"(x10.z), "=f"(x10.w) : "r"(a1 + in0));
-                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x11.x), "=f"(x11.y), "=f"(x11.z), "=f"(x11.w) : "r"(a1 + in1));
+                // all four atom pairs of this warp are read first (16 x 128-bit loads in flight per lane), then converted
+                // and written back: one atom pair at a time left the warp waiting on its own loads and dependency chains
+                // (round 2's ncu: the transform warps were busy ~80 % of the time at an IPC of 0.25)
+                float4 x[16 / NTW][4];
+#pragma unroll
+                for (int k = 0; k < 16 / NTW; ++k) {
+                    const uint32_t a0 = base + (uint32_t)(tw + k * NTW) * 1024u, a1 = a0 + (uint32_t)kTcSlabBytes;
+                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x[k][0].x), "=f"(x[k][0].y), "=f"(x[k][0].z), "=f"(x[k][0].w) : "r"(a0 + in0));
+                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x[k][1].x), "=f"(x[k][1].y), "=f"(x[k][1].z), "=f"(x[k][1].w) : "r"(a0 + in1));
+                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x[k][2].x), "=f"(x[k][2].y), "=f"(x[k][2].z), "=f"(x[k][2].w) : "r"(a1 + in0));
+                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x[k][3].x), "=f"(x[k][3].y), "=f"(x[k][3].z), "=f"(x[k][3].w) : "r"(a1 + in1));
+                }
+                __syncwarp(); // every lane has read its atoms before any lane overwrites them
+#pragma unroll
+                for (int k = 0; k < 16 / NTW; ++k) {
+                    const uint32_t a0 = base + (uint32_t)(tw + k * NTW) * 1024u, a1 = a0 + (uint32_t)kTcSlabBytes;
                     uint4 h0, l0, h1, l1;
-                    split_f16x8(x00, x01, h0, l0);
-                    split_f16x8(x10, x11, h1, l1);
-                    __syncwarp(); // every lane has read both atoms before any lane overwrites them
+                    split_f16x8(x[k][0], x[k][1], h0, l0);
+                    split_f16x8(x[k][2], x[k][3], h1, l1);
                     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a0 + out0), "r"(h0.x), "r"(h0.y), "r"(h0.z), "r"(h0.w) : "memory");
                     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a0 + out1), "r"(h1.x), "r"(h1.y), "r"(h1.z), "r"(h1.w) : "memory");
                     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a1 + out0), "r"(l0.x), "r"(l0.y), "r"(l0.z), "r"(l0.w) : "memory");
