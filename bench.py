@@ -80,6 +80,7 @@ class ClockSampler(threading.Thread):
         self.active = False  # set by the main thread around the timed regions: nothing is queried outside them
         self.max_mhz = None
         self.ok = False
+        self.first_delay_s = float(os.environ.get("LWC_BENCH_SAMPLER_DELAY_US", "300")) * 1e-6
         try:
             import pynvml
 
@@ -101,10 +102,19 @@ class ClockSampler(threading.Thread):
             getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
             getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
         }
+        was_active = False
         while not self.stop_flag:
             if not self.active:
-                time.sleep(0.0005)
+                was_active = False
+                time.sleep(0.0002)
                 continue
+            if not was_active:
+                # first sample of a timed region: let the launching thread enqueue its work first (an NVML query takes
+                # driver locks; colliding with the first launches of a 1.3 ms region costs microseconds per step)
+                was_active = True
+                time.sleep(self.first_delay_s)
+                if not self.active:
+                    continue
             try:
                 mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
                 util = 1
@@ -406,7 +416,9 @@ def run_b200(args):
     sampler.active = True
     with torch.cuda.stream(stream):
         ev0.record(stream)
+        t_enq = time.perf_counter()
         run_timed()
+        enqueue_ms = (time.perf_counter() - t_enq) * 1e3
         ev1.record(stream)
     barrier()
     sampler.active = False
@@ -509,6 +521,7 @@ def run_b200(args):
                                 "programmatic dependent launch: a launch streams its (resident) inputs while the previous one drains")
                                + "; the K timed launches are one lwc_score_batches call"},
         "clocks": sampler.summary(), "per_rank_ms_per_step": per_rank_ms, "per_rank_spread": spread,
+        "host_enqueue_ms": enqueue_ms,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "wall_ms_per_step": wall_ms / e2e_steps,
                 "api": "lwc_score_batch(LWC_MEM_HOST), pinned host buffers",
