@@ -350,31 +350,37 @@ def run_b200(args):
                 (("conf", (R, N), np.float32), ("cw", (R, N), np.float32), ("agree", (R, M), np.float32),
                  ("winner", (R,), np.int32), ("rank", (R, N), np.int32))}
 
-    n_rot = 3
+    # Distinct input batches: a fused launch walks up to 32 batches at once with different CTAs in different batches,
+    # so every batch of such a run must be its own memory (two list entries sharing a buffer would be read
+    # concurrently and meet in L2); across runs, and with one launch per batch, any three batches of 403 MB already
+    # defeat the 126 MB L2.
+    n_rot = 3 if (args.launch == "loop" or os.environ.get("LWC_LIST_FUSION") == "0") else max(3, min(args.steps, 32))
     dE = [torch.empty((R, N, D), dtype=torch.float32, device="cuda") for _ in range(n_rot)]
     dE[0].copy_(torch.from_numpy(hE.array))
     for i in range(1, n_rot):  # distinct data per rotating batch: a request-wise roll of batch 0
         dE[i].copy_(torch.roll(dE[0], shifts=i * 17, dims=0))
     dV = torch.from_numpy(V).cuda()
     dw = torch.from_numpy(w).cuda()
-    d_out = {"conf": torch.empty((R, N), dtype=torch.float32, device="cuda"),
-             "cw": torch.empty((R, N), dtype=torch.float32, device="cuda"),
-             "agree": torch.empty((R, M), dtype=torch.float32, device="cuda"),
-             "winner": torch.empty((R,), dtype=torch.int32, device="cuda"),
-             "rank": torch.empty((R, N), dtype=torch.int32, device="cuda")}
+    d_outs = [{"conf": torch.empty((R, N), dtype=torch.float32, device="cuda"),
+               "cw": torch.empty((R, N), dtype=torch.float32, device="cuda"),
+               "agree": torch.empty((R, M), dtype=torch.float32, device="cuda"),
+               "winner": torch.empty((R,), dtype=torch.int32, device="cuda"),
+               "rank": torch.empty((R, N), dtype=torch.int32, device="cuda")} for _ in range(n_rot)]
+    d_out = d_outs[0]
     desc_dev = lwc_b200.BatchDesc(R, N, D, M, lwc_b200.SIM_COSINE, lwc_b200.PREC_FP32, lwc_b200.MEM_DEVICE, 1)
     desc_host = lwc_b200.BatchDesc(R, N, D, M, lwc_b200.SIM_COSINE, lwc_b200.PREC_FP32, lwc_b200.MEM_HOST, 1)
     stream = torch.cuda.Stream()
 
     # The timed region is ONE call of lwc_score_batches with a list of K batches (the three resident batches in
-    # rotation): the launches are enqueued by a C loop under one lock, so the overlap of consecutive launches
-    # does not depend on how fast this interpreter comes round (round 1: 0.87 scaling efficiency at 8 GPUs with
-    # K = 20, because eight Python loops contended for the launch path).
+    # rotation).  The library scores a run of same-shaped batches with one launch per 32 batches (persistent CTAs
+    # walk the run), so nothing depends on how fast this interpreter -- or the launch path eight ranks share --
+    # comes round (round 1: 0.87 scaling efficiency at 8 GPUs with K = 20).  LWC_LIST_FUSION=0 restores one launch
+    # per batch, --launch loop one library call per batch.
     def batch_list(k):
         return ctx.batch_list([desc_dev] * k, [dE[j % n_rot].data_ptr() for j in range(k)], [dV.data_ptr()] * k,
-                              [dw.data_ptr()] * k, [d_out["conf"].data_ptr()] * k, [d_out["cw"].data_ptr()] * k,
-                              [d_out["agree"].data_ptr()] * k, [d_out["winner"].data_ptr()] * k,
-                              [d_out["rank"].data_ptr()] * k, stream=stream.cuda_stream)
+                              [dw.data_ptr()] * k, *[[d_outs[j % n_rot][o].data_ptr() for j in range(k)]
+                                                     for o in ("conf", "cw", "agree", "winner", "rank")],
+                              stream=stream.cuda_stream)
 
     run_warm, run_timed, run_one = batch_list(args.warmup), batch_list(args.steps), batch_list(1)
     if args.launch == "loop":  # A/B: one lwc_score_batch call per step from this interpreter (round 1's timed loop)
@@ -516,10 +522,11 @@ def run_b200(args):
         "config": {"workload": workload_string(R, N, D, M),
                    "similarity": "cosine", "precision": "fp32-grade (3xTF32 compensated Gram)",
                    "kernel": kernel, "parallelism": f"request-sharded x{world}, no collectives",
-                   "l2": f"{n_rot} rotating input batches of {hE.nbytes / 1e6:.0f} MB each (> 126 MB L2)",
+                   "l2": f"{n_rot} distinct input batches of {hE.nbytes / 1e6:.0f} MB each, visited in rotation (> 126 MB L2; no buffer "
+                         "appears twice in one fused launch)",
                    "launches": ("serialised" if args.no_overlap else
                                 "programmatic dependent launch: a launch streams its (resident) inputs while the previous one drains")
-                               + "; the K timed launches are one lwc_score_batches call"},
+                               + "; the K timed steps are one lwc_score_batches call: a run of same-shaped batches is scored by one launch per 32 batches"},
         "clocks": sampler.summary(), "per_rank_ms_per_step": per_rank_ms, "per_rank_spread": spread,
         "host_enqueue_ms": enqueue_ms,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -529,9 +536,13 @@ def run_b200(args):
                 "bound": "PCIe: plain pinned cudaMemcpyAsync H2D of the same bytes on this box = h2d_peak_gbs",
                 "other_transports": transports or None},
         "gpu_launches": int(launches),
+        # per STEP (one batch): a fused launch scores steps_per_launch batches, so bytes and time both scale with it
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": load_traffic(kernel, R), "kernel": kernel, "peak_source": peak_src,
-                     "bytes_per_launch": bytes_per_launch, "frac_of_nominal_8000": achieved / 8000.0},
+                     "bytes_per_launch": bytes_per_launch * args.steps / max(int(launches), 1),
+                     "bytes_per_step": bytes_per_launch, "steps_per_launch": args.steps / max(int(launches), 1),
+                     "traffic_is": "DRAM bytes per step (batch) from the committed ncu capture",
+                     "frac_of_nominal_8000": achieved / 8000.0},
         "host_device_paths_agree": same,
     }
     if rank == 0:
@@ -614,6 +625,15 @@ def timed_side_shape(torch, lwc_b200, synth, ctx, dist, R, N, D, M, prec, steps,
     parity sample of the outputs.  Returns (ms_per_step, kernel name, parity dict or None)."""
     from lwc_b200 import shard
 
+    # side shapes rotate one or two big batches: a fused launch would read the same buffer from several CTAs at once
+    # (L2 hits), so these are timed with one launch per batch
+    prev = os.environ.get("LWC_LIST_FUSION")
+    os.environ["LWC_LIST_FUSION"] = "0"
+    ctx = lwc_b200.Context(device=torch.cuda.current_device())
+    if prev is None:
+        os.environ.pop("LWC_LIST_FUSION", None)
+    else:
+        os.environ["LWC_LIST_FUSION"] = prev
     kernel = ctx.kernel_for(R, N, D, M, precision=prec)
     dE = [device_batch(torch, R, N, D, seed + i) for i in range(n_rot)]
     V = synth.votes(R, N, M, seed=11)
@@ -654,6 +674,7 @@ def timed_side_shape(torch, lwc_b200, synth, ctx, dist, R, N, D, M, prec, steps,
         par = parity_sample(oracle, dE[j][:n].cpu().numpy(), V[:n], w[:n], got, rtol=2e-3 if tf32 else 1e-5,
                             atol=1e-5 if tf32 else 1e-7)
     del dE, outs
+    ctx.close()
     torch.cuda.empty_cache()
     return ms, kernel, par
 

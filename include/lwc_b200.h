@@ -181,11 +181,16 @@ int32_t lwc_stage_f64_bf16(lwc_ctx *ctx, const double *src, size_t n, uint16_t *
  * device-resident batches, enqueued back to back on `stream` inside one call.  descs [n_batches]; every
  * other argument is an array of n_batches pointers with lwc_score_batch's meaning (an output array, or an
  * entry of one, may be NULL).  Every batch must be LWC_MEM_DEVICE.  The list is validated before the first
- * launch: a 400 means nothing was enqueued.  Results are bit-identical to n_batches single calls; what
- * changes is the host side -- one lock, one argument check and one library call per list instead of per
- * batch -- so a producer that already holds several batches in HBM keeps the GPU's launch queue full
- * (with LWC_CTX_INPUTS_RESIDENT consecutive launches overlap only while the host stays a launch ahead of
- * a ~60 us kernel).  Asynchronous on `stream` like a device-memory lwc_score_batch. */
+ * launch: a 400 means nothing was enqueued.  Results are bit-identical to n_batches single calls.  What
+ * changes: (1) one lock, one argument check and one library call per list instead of per batch; (2) a RUN
+ * of consecutive entries with the same descriptor that take the small-pool ring kernel (N <= 32, cosine)
+ * is scored by ONE launch per 32 batches -- its persistent CTAs walk the whole run, so launch latency, the
+ * first bytes' latency and the last requests' tail are paid once per run instead of once per batch, and
+ * nothing depends on the host staying a launch ahead of a ~60 us kernel (cfg2: 63.1 us per batch = 0.99 of
+ * the measured HBM peak at 20 batches per call, against 66.5 us = 0.94 launched one by one).  Entries of
+ * one list must not share output buffers (inside a fused launch their order is undefined); the
+ * environment variable LWC_LIST_FUSION=0 restores one launch per batch.  Asynchronous on `stream` like a
+ * device-memory lwc_score_batch. */
 int32_t lwc_score_batches(lwc_ctx *ctx, int32_t n_batches, const lwc_batch_desc *descs, const float *const *E,
                           const float *const *V, const float *const *w, float *const *conf, float *const *cw,
                           float *const *agree, int32_t *const *winner, int32_t *const *rank, void *stream);

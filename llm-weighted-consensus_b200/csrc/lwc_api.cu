@@ -261,8 +261,9 @@ cudaError_t ensure_fix_flags(lwc_ctx *ctx, int R) {
     return e;
 }
 
+// list != nullptr: one launch over a list of same-shaped batches (score_stream_list_kernel); p.R = all requests of the list
 template <int NT, bool X3, int NCW, int NF>
-cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
+cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st, const lwc::ScoreList *list = nullptr) {
     using C = lwc::StreamCfg<NT, X3, NCW, NF>;
     const size_t avail = (size_t)ctx->max_smem_optin - 128 - C::fixed_bytes();
     lwc::StreamGeom geo;
@@ -281,6 +282,9 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
     if (!configured[ctx->device & 63]) {
         cudaError_t e = cudaFuncSetAttribute(lwc::score_stream_kernel<NT, X3, NCW, NF>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(lwc::score_stream_list_kernel<NT, X3, NCW, NF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     ctx->max_smem_optin);
         if (e != cudaSuccess) return e;
         configured[ctx->device & 63] = true;
     }
@@ -295,6 +299,7 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    if (list) return cudaLaunchKernelEx(&cfg, lwc::score_stream_list_kernel<NT, X3, NCW, NF>, p, geo, *list);
     return cudaLaunchKernelEx(&cfg, lwc::score_stream_kernel<NT, X3, NCW, NF>, p, geo);
 }
 
@@ -338,6 +343,22 @@ SmallRoute small_route(const lwc_ctx *ctx, const Plan &pl) {
         r.stream = !(pl.np == 32 && pl.x3); // 32-row fp32-grade pools: the direct kernel is faster on either kind of pieces
     r.f16 = f16_ok && !r.stream;
     return r;
+}
+
+// One launch for a run of same-shaped batches on the ring kernel (default consumer / finaliser counts only).
+// Returns false when this shape does not take that route: the caller then launches batch by batch.
+bool list_route(const lwc_ctx *ctx, const Plan &pl) {
+    return pl.route == ROUTE_SMALL && small_route(ctx, pl).stream && ctx->stream_ncw == 0 && ctx->stream_nf == 0;
+}
+int launch_list(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, const lwc::ScoreList &list, cudaStream_t st) {
+    cudaError_t e;
+    if (pl.np == 16)
+        e = pl.x3 ? launch_stream_one<16, true, 12, 4>(ctx, p, st, &list) : launch_stream_one<16, false, 12, 4>(ctx, p, st, &list);
+    else
+        e = pl.x3 ? launch_stream_one<32, true, 8, 2>(ctx, p, st, &list) : launch_stream_one<32, false, 8, 2>(ctx, p, st, &list);
+    if (e != cudaSuccess) return fail(ctx, LWC_ERR_INTERNAL, "kernel launch (%s, list of %d) failed: %s", pl.name, list.n, cudaGetErrorString(e));
+    ctx->launches++;
+    return LWC_OK;
 }
 
 int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStream_t st) {
@@ -553,6 +574,7 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     if (const char *s = getenv("LWC_STREAM_NF")) ctx->stream_nf = atoi(s);
     if (const char *s = getenv("LWC_POOL_NO_P2P")) ctx->no_p2p = atoi(s);
     if (const char *s = getenv("LWC_CHUNK_REQUESTS")) ctx->chunk_requests = atoi(s);
+    if (const char *s = getenv("LWC_LIST_FUSION")) ctx->no_list_fusion = atoi(s) == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_TC_KO")) ctx->tc_ko = atoi(s);
     if (const char *s = getenv("LWC_TC_X3")) ctx->tc_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_X3")) ctx->small_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
@@ -759,9 +781,17 @@ int32_t lwc_score_batches(lwc_ctx *ctx, int32_t n_batches, const lwc_batch_desc 
     }
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
-    for (int32_t b = 0; b < n_batches; ++b) {
+    auto same_shape = [&](int32_t a, int32_t b) {
+        const lwc_batch_desc &x = descs[a], &y = descs[b];
+        return x.R == y.R && x.N == y.N && x.D == y.D && x.M == y.M && x.similarity == y.similarity && x.precision == y.precision &&
+               x.w_per_request == y.w_per_request;
+    };
+    for (int32_t b = 0; b < n_batches;) {
         const lwc_batch_desc &d = descs[b];
-        if (d.R == 0) continue;
+        if (d.R == 0) {
+            ++b;
+            continue;
+        }
         const Plan pl = plan_for(d, E ? E[b] : nullptr);
         lwc::ScoreParams p;
         p.E = E ? E[b] : nullptr, p.V = V ? V[b] : nullptr, p.w = w ? w[b] : nullptr;
@@ -775,8 +805,32 @@ int32_t lwc_score_batches(lwc_ctx *ctx, int32_t n_batches, const lwc_batch_desc 
             p.inputs_resident = 0;
             ctx->weights_in_flight = 0;
         }
-        const int rc = launch_plan(ctx, pl, p, st);
-        if (rc) return rc;
+        // A run of same-shaped batches on the ring kernel becomes ONE launch (up to kMaxList batches): the persistent
+        // CTAs walk the whole run, so nothing is lost between batches (launch latency, the first bytes' latency, the
+        // last requests' tail) and nothing depends on the host keeping ahead of the GPU.  Results are the bits of
+        // single launches: a request's arithmetic does not depend on where in a launch it sits.
+        int32_t run = 1;
+        if (list_route(ctx, pl) && d.similarity == LWC_SIM_COSINE && !ctx->no_list_fusion)
+            while (b + run < n_batches && run < lwc::kMaxList && same_shape(b, b + run) &&
+                   plan_for(descs[b + run], E[b + run]).route == pl.route && (long long)(run + 1) * d.R < 0x7fffffffLL)
+                ++run;
+        if (run > 1) {
+            lwc::ScoreList list;
+            list.n = run, list.R_each = d.R;
+            for (int32_t k = 0; k < run; ++k) {
+                list.E[k] = E[b + k], list.V[k] = V ? V[b + k] : nullptr, list.w[k] = w ? w[b + k] : nullptr;
+                list.conf[k] = conf ? conf[b + k] : nullptr, list.cw[k] = cw ? cw[b + k] : nullptr;
+                list.agree[k] = agree ? agree[b + k] : nullptr, list.winner[k] = winner ? winner[b + k] : nullptr;
+                list.rank[k] = rank ? rank[b + k] : nullptr;
+            }
+            p.R = run * d.R;
+            const int rc = launch_list(ctx, pl, p, list, st);
+            if (rc) return rc;
+        } else {
+            const int rc = launch_plan(ctx, pl, p, st);
+            if (rc) return rc;
+        }
+        b += run;
     }
     return LWC_OK;
 }

@@ -63,6 +63,7 @@ struct lwc_ctx {
     size_t table_cap[5] = {0};
     long long table_rows = 0;
     int table_D = 0, table_M = 0;
+    int no_list_fusion = 0;    // LWC_LIST_FUSION=0: lwc_score_batches launches batch by batch even where one launch could take a run
     int weights_in_flight = 0; // lwc_table_weights(LWC_MEM_DEVICE) has queued a kernel that writes a caller's `w`: the next
                                // lwc_score_batch must not let its input reads run ahead of the stream (LWC_CTX_INPUTS_RESIDENT)
     void *typed_buf = nullptr; // fp32 copy of device-resident f64 / bf16 embeddings (lwc_score_batch_typed)

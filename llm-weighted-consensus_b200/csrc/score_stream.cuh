@@ -117,9 +117,30 @@ struct StreamCfg {
 constexpr bool kStreamFlush = kMmaChain < (1 << 20); // A/B builds (-DLWC_MMA_CHAIN=1000000) compile the flush out
 constexpr int kVotePrefetch = 4; // voters whose rows a finaliser keeps in registers
 
-template <int NT, bool X3, int NCW, int NFIN>
-__global__ void __launch_bounds__((1 + NCW + NFIN) * 32, 1)
-score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
+// A list of same-shaped batches scored by ONE launch (lwc_score_batches): request g of the launch is request
+// g % R_each of batch g / R_each.  Passed by value as a kernel parameter (constant bank), so no device allocation or
+// copy is needed for it.
+constexpr int kMaxList = 32;
+struct ScoreList {
+    int n, R_each;
+    const float *E[kMaxList], *V[kMaxList], *w[kMaxList];
+    float *conf[kMaxList], *cw[kMaxList], *agree[kMaxList];
+    int32_t *winner[kMaxList], *rank[kMaxList];
+};
+
+// `p` with the pointers of the batch that holds launch-wide request g; *r = g's index inside that batch
+__device__ __forceinline__ ScoreParams list_params(const ScoreParams &p, const ScoreList *list, int g, int *r) {
+    ScoreParams q = p;
+    const int b = g / list->R_each;
+    *r = g - b * list->R_each;
+    q.E = list->E[b], q.V = list->V[b], q.w = list->w[b];
+    q.conf = list->conf[b], q.cw = list->cw[b], q.agree = list->agree[b];
+    q.winner = list->winner[b], q.rank = list->rank[b];
+    return q;
+}
+
+template <int NT, bool X3, int NCW, int NFIN, bool LIST>
+__device__ __forceinline__ void score_stream_body(const ScoreParams &p, const StreamGeom &geo, const ScoreList *list) {
     using C = StreamCfg<NT, X3, NCW, NFIN>;
     constexpr int RPL = C::RPL, MT = C::MT, NTL = C::NTL, NF = C::NF;
     constexpr int TPITCH = C::TPITCH, NACC = C::NACC, MAXS = C::MAXS;
@@ -171,7 +192,14 @@ score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
         int slot = 0;
         uint32_t phase = 0;
         for (int q = 0; q < nreq; ++q) {
-            const float *Er = p.E + (size_t)(r_begin + q) * N * D;
+            const float *Er;
+            if (LIST) {
+                int rl;
+                const ScoreParams pb = list_params(p, list, r_begin + q, &rl);
+                Er = pb.E + (size_t)rl * N * D;
+            } else {
+                Er = p.E + (size_t)(r_begin + q) * N * D;
+            }
             for (int s = 0; s < spr; ++s) {
                 mbar_wait(empty0 + 8 * slot, phase ^ 1u);
                 const int kv = min(KS, D - s * KS);
@@ -322,8 +350,13 @@ score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
     float *tile = tiles + (size_t)f * NT * TPITCH;
     float pv[kVotePrefetch], pw[kVotePrefetch];
     auto prefetch_votes = [&](int r) {
-        const float *Vr = p.V + (size_t)r * M * N;
-        const float *wr = p.w + (p.w_per_request ? (size_t)r * M : 0);
+        ScoreParams pb = p;
+        if (LIST) {
+            const int g = r;
+            pb = list_params(p, list, g, &r);
+        }
+        const float *Vr = pb.V + (size_t)r * M * N;
+        const float *wr = pb.w + (pb.w_per_request ? (size_t)r * M : 0);
 #pragma unroll
         for (int m = 0; m < kVotePrefetch; ++m) {
             pv[m] = (m < M && lane < N) ? __ldg(Vr + (size_t)m * N + lane) : 0.f;
@@ -400,10 +433,29 @@ score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
                     }
                 }
         __syncwarp();
-        warp_tally_and_rank_pf<kVotePrefetch, NT>(p, r, tile, TPITCH, lane, pv, pw);
+        if (LIST) {
+            int rl;
+            const ScoreParams pb = list_params(p, list, r, &rl);
+            warp_tally_and_rank_pf<kVotePrefetch, NT>(pb, rl, tile, TPITCH, lane, pv, pw);
+        } else {
+            warp_tally_and_rank_pf<kVotePrefetch, NT>(p, r, tile, TPITCH, lane, pv, pw);
+        }
         __syncwarp();
         if (q + NF < nreq) prefetch_votes(r + NF);
     }
+}
+
+template <int NT, bool X3, int NCW, int NFIN>
+__global__ void __launch_bounds__((1 + NCW + NFIN) * 32, 1)
+score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
+    score_stream_body<NT, X3, NCW, NFIN, false>(p, geo, nullptr);
+}
+
+// p.R = list.n * list.R_each; p's own pointers are unused
+template <int NT, bool X3, int NCW, int NFIN>
+__global__ void __launch_bounds__((1 + NCW + NFIN) * 32, 1)
+score_stream_list_kernel(const ScoreParams p, const StreamGeom geo, const __grid_constant__ ScoreList list) {
+    score_stream_body<NT, X3, NCW, NFIN, true>(p, geo, &list);
 }
 
 } // namespace lwc

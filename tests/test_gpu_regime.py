@@ -356,3 +356,54 @@ def test_small_pool_fp16_pieces_fall_back_outside_fp16_range(lwc, oracle):
                 os.environ["LWC_SMALL_X3"] = old
         assert compare(got, want, V) == 1.0, env
         properties_hold(got, V)
+
+
+@pytest.mark.parametrize("shape,prec", [((600, 16, 1536, 4), "fp32"), ((450, 32, 1024, 4), "tf32"), ((300, 9, 772, 3), "fp32")],
+                         ids=["cfg2_shape", "n32_tf32", "ragged"])
+def test_a_run_of_same_shaped_batches_is_one_launch_with_the_same_bits(lwc, oracle, shape, prec):
+    """lwc_score_batches turns a run of same-shaped ring-kernel batches into ONE launch whose persistent CTAs walk
+    the whole run (request g = request g % R of batch g / R).  Launch count, bit-equality with single calls, and
+    LWC_LIST_FUSION=0 (batch-by-batch launches) as the A/B."""
+    R, N, D, M = shape
+    K = 5
+    p = lwc.PREC_FP32 if prec == "fp32" else lwc.PREC_TF32
+    batches = [fast_batch(R, N, D, M, seed=700 + i) for i in range(K)]
+    for fusion in ("1", "0"):
+        old = os.environ.get("LWC_LIST_FUSION")
+        os.environ["LWC_LIST_FUSION"] = fusion
+        try:
+            with lwc.Context(device=0, flags=lwc.CTX_INPUTS_RESIDENT) as c:
+                singles = [c.score_batch_device(E, V, w, precision=p) for E, V, w in batches]
+                keep, ptrs = [], {k: [] for k in ("E", "V", "w", "conf", "cw", "agree", "winner", "rank")}
+                for E, V, w in batches:
+                    bufs = {"E": lwc.DeviceBuffer(c, E.nbytes).upload(E), "V": lwc.DeviceBuffer(c, V.nbytes).upload(V),
+                            "w": lwc.DeviceBuffer(c, w.nbytes).upload(w), "conf": lwc.DeviceBuffer(c, 4 * R * N),
+                            "cw": lwc.DeviceBuffer(c, 4 * R * N), "agree": lwc.DeviceBuffer(c, 4 * R * M),
+                            "winner": lwc.DeviceBuffer(c, 4 * R), "rank": lwc.DeviceBuffer(c, 4 * R * N)}
+                    keep.append(bufs)
+                    for k in ptrs:
+                        ptrs[k].append(bufs[k].ptr)
+                descs = [lwc.BatchDesc(R, N, D, M, lwc.SIM_COSINE, p, lwc.MEM_DEVICE, 1)] * K
+                run = c.batch_list(descs, *[ptrs[k] for k in ("E", "V", "w", "conf", "cw", "agree", "winner", "rank")])
+                n0 = c.launch_count()
+                run()
+                run()  # twice: the second list overlaps the first (programmatic dependent launch) and must win
+                c.synchronize()
+                assert c.launch_count() - n0 == (2 if fusion == "1" else 2 * K)
+                for bufs, want in zip(keep, singles):
+                    got = {"conf": bufs["conf"].download((R, N), np.float32), "cw": bufs["cw"].download((R, N), np.float32),
+                           "agree": bufs["agree"].download((R, M), np.float32), "winner": bufs["winner"].download((R,), np.int32),
+                           "rank": bufs["rank"].download((R, N), np.int32)}
+                    for k in got:
+                        assert np.array_equal(got[k], want[k], equal_nan=True), (k, fusion)
+                for bufs in keep:
+                    for b in bufs.values():
+                        b.free()
+        finally:
+            if old is None:
+                os.environ.pop("LWC_LIST_FUSION", None)
+            else:
+                os.environ["LWC_LIST_FUSION"] = old
+    want = oracle.score_f64(*batches[0], oracle.SIM_COSINE)
+    if prec == "fp32":
+        assert compare(singles[0], want, batches[0][1]) == 1.0
