@@ -148,6 +148,23 @@ cudaError_t launch_small_one(const lwc::ScoreParams &p, cudaStream_t st) {
     return cudaGetLastError();
 }
 
+// the cfg3 route: 32-row fp32-grade pools, fp16 pieces, loads pipelined through PS shared-memory stages
+template <int PS>
+cudaError_t launch_small_pipe32(const lwc::ScoreParams &p, cudaStream_t st) {
+    constexpr size_t smem = lwc::small_smem_bytes<32, true, 2, 2, PS>();
+    static std::atomic<bool> configured[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_small_kernel<32, true, 2, 2, true, PS>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured[dev & 63] = true;
+    }
+    lwc::score_small_kernel<32, true, 2, 2, true, PS><<<p.R, 64, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
 // f16: fp32-grade route on fp16 pieces (default for X3; LWC_SMALL_X3=tf32 keeps tf32 pieces)
 template <int NT, bool X3>
 cudaError_t launch_small(const lwc::ScoreParams &p, cudaStream_t st, int kw, int u, bool f16) {
@@ -376,6 +393,8 @@ int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStr
         if (pl.np == 16)
             e = pl.x3 ? launch_small<16, true>(p, st, ctx->small_kw, ctx->small_u, sr.f16)
                       : launch_small<16, false>(p, st, ctx->small_kw, ctx->small_u, false);
+        else if (pl.x3 && sr.f16 && !ctx->small_kw_set && ctx->small_u == 0 && ctx->small_pipe != 0) // the cfg3 route
+            e = ctx->small_pipe == 3 ? launch_small_pipe32<3>(p, st) : launch_small_pipe32<4>(p, st);
         else // 32-row pools: 2 warps per request measured best (1.157 vs 1.185 ms at KW=4, cfg3 slice)
             e = pl.x3 ? launch_small<32, true>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u, sr.f16)
                       : launch_small<32, false>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u, false);
@@ -578,6 +597,7 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     if (const char *s = getenv("LWC_TC_KO")) ctx->tc_ko = atoi(s);
     if (const char *s = getenv("LWC_TC_X3")) ctx->tc_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_X3")) ctx->small_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
+    if (const char *s = getenv("LWC_SMALL_PIPE")) ctx->small_pipe = atoi(s);
     if (const char *s = getenv("LWC_TC_STAGES")) ctx->tc_stages = atoi(s);
     if (ctx->stream_ncw != 0 && ctx->stream_ncw != 4 && ctx->stream_ncw != 8 && ctx->stream_ncw != 12) ctx->stream_ncw = 0;
     if (ctx->stream_kc < 0 || ctx->stream_kc % 16) ctx->stream_kc = 0;

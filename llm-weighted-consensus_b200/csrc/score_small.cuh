@@ -48,6 +48,8 @@ struct SmallCfg {
     static constexpr int NACC = (MT * NTL + (X3 ? MT * NTL : 0)) * 4;
     // HH fragment registers per lane that are actually accumulated (upper blocks of the symmetric tile)
     static constexpr int NHH = (MT == 1 ? NTL : NTL + (NTL - 2)) * 4;
+    // floats of the areas below (red, tile, flush), rounded up to 16 bytes: where the optional load pipeline starts
+    static constexpr int PIPE_OFF_FLOATS = (((KW - 1) * NACC * 32 + NT * PITCH + (X3 ? KW * NHH * 32 : 0)) + 3) / 4 * 4;
     static constexpr size_t smem_bytes() {
         size_t red = (size_t)(KW - 1) * NACC * 32 * sizeof(float);
         size_t tile = (size_t)NT * PITCH * sizeof(float);
@@ -55,6 +57,11 @@ struct SmallCfg {
         return red + tile + flush;
     }
 };
+
+template <int NT, bool X3, int KW, int U, int PS>
+constexpr size_t small_smem_bytes() {
+    return (size_t)SmallCfg<NT, X3, KW, U>::PIPE_OFF_FLOATS * 4 + (size_t)KW * PS * U * (NT / 8) * 32 * 16;
+}
 
 // The tensor core's fp32 accumulator truncates when it aligns addends (measured on this part: ~1.1e-8 relative
 // drift per accumulated MMA on same-sign sums such as the diagonal |E_i|^2), so an fp32-grade route must not let
@@ -246,6 +253,145 @@ __device__ __forceinline__ void small_gram(const ScoreParams &p, int r, float *r
     }
 }
 
+// 16-byte asynchronous global -> shared copy (L2 only); src_bytes = 0 writes zeros without reading
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, int src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// The fp16-piece Gram pass with the loads software-pipelined through shared memory (fp32-grade route only).
+// The direct form above keeps U chunks per warp in flight in registers: at 128 registers 16 warps fit an SM, 64 KB in
+// flight, and ncu showed the kernel waiting on its own loads (long-scoreboard stall 6.9, issue slots 36 %).  Here every
+// lane owns PS private 16-byte slots per (chunk, row group): it issues cp.async for the chunks PS-1 iterations ahead,
+// waits for the oldest group and reads back exactly the bytes it asked for -- no cross-lane synchronisation, no
+// bank conflicts (consecutive lanes, consecutive 16 bytes), and the registers hold one iteration's data only.
+template <int NT, int KW, int U, int PS>
+__device__ __forceinline__ void small_gram_pipe(const ScoreParams &p, int r, float *red, float *fl, float4 *pipe,
+                                                float (&hh)[NT / 16][NT / 8][4], float (&hl)[NT / 16][NT / 8][4]) {
+    using C = SmallCfg<NT, true, KW, U>;
+    constexpr int RPL = C::RPL, MT = C::MT, NTL = C::NTL;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int N = p.N, D = p.D;
+    const float *Er = p.E + (size_t)r * N * D;
+    const float *rowp[RPL];
+    bool rv[RPL];
+#pragma unroll
+    for (int q = 0; q < RPL; ++q) {
+        const int row = g + 8 * q;
+        rv[q] = row < N;
+        rowp[q] = Er + (size_t)(rv[q] ? row : 0) * D + 4 * t;
+    }
+    const int nchunk = (D + 15) >> 4;
+    const int n_it = (nchunk - warp * U + KW * U - 1) / (KW * U); // iterations of this warp (<= 0: none)
+    constexpr int kFlushIters = kMmaChain / U > 0 ? kMmaChain / U : 1; // one MMA per accumulator and chunk
+    // this lane's slots: [warp][stage][u][q][lane]
+    float4 *mine = pipe + (size_t)warp * PS * U * RPL * 32 + lane;
+    const uint32_t mine_u32 = (uint32_t)__cvta_generic_to_shared(mine);
+    auto issue = [&](int it) {
+        if (it < n_it) {
+            const int c0 = warp * U + it * KW * U;
+            const uint32_t base = mine_u32 + (uint32_t)((it % PS) * U * RPL * 32 * 16);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int k = (c0 + u) * 16 + 4 * t;
+#pragma unroll
+                for (int q = 0; q < RPL; ++q) {
+                    const bool ok = rv[q] && k < D;
+                    cp_async16(base + (uint32_t)((u * RPL + q) * 32 * 16), ok ? (const void *)(rowp[q] + (size_t)(c0 + u) * 16) : (const void *)Er,
+                               ok ? 16 : 0);
+                }
+            }
+        }
+        cp_async_commit(); // an empty group keeps the group count uniform
+    };
+#pragma unroll
+    for (int s = 0; s < C::NHH; ++s) fl[s * 32] = 0.f;
+#pragma unroll
+    for (int it = 0; it < PS - 1; ++it) issue(it);
+    for (int it = 0; it < n_it; ++it) {
+        issue(it + PS - 1);
+        cp_async_wait<PS - 1>(); // the group of iteration `it` has landed
+        const float4 *slot = mine + (size_t)(it % PS) * U * RPL * 32;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            uint32_t h01[RPL], h23[RPL], l01[RPL], l23[RPL];
+#pragma unroll
+            for (int q = 0; q < RPL; ++q) split_f16x4(slot[(u * RPL + q) * 32], h01[q], h23[q], l01[q], l23[q]);
+#pragma unroll
+            for (int a = 0; a < MT; ++a) {
+#pragma unroll
+                for (int b = 0; b < NTL; ++b) {
+                    if (b >= 2 * a)
+                        mma_m16n8k16_f16(hh[a][b], h01[2 * a], h01[2 * a + 1], h23[2 * a], h23[2 * a + 1], h01[b], h23[b]);
+                    mma_m16n8k16_f16(hl[a][b], h01[2 * a], h01[2 * a + 1], h23[2 * a], h23[2 * a + 1], l01[b], l23[b]);
+                }
+            }
+        }
+        if ((it + 1) % kFlushIters == 0 && it + 1 < n_it) {
+            int s = 0;
+#pragma unroll
+            for (int a = 0; a < MT; ++a)
+#pragma unroll
+                for (int b = 0; b < NTL; ++b)
+                    if (b >= 2 * a) {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            fl[s * 32] += hh[a][b][e];
+                            hh[a][b][e] = 0.f;
+                            ++s;
+                        }
+                    }
+        }
+    }
+    cp_async_wait<0>();
+    {
+        int s = 0;
+#pragma unroll
+        for (int a = 0; a < MT; ++a)
+#pragma unroll
+            for (int b = 0; b < NTL; ++b)
+                if (b >= 2 * a) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) hh[a][b][e] += fl[(s++) * 32];
+                }
+    }
+    // ---- K-split reduction, as small_gram
+    if (KW > 1) {
+        if (warp > 0) {
+            float *dst = red + (size_t)(warp - 1) * C::NACC * 32 + lane;
+            int s = 0;
+#pragma unroll
+            for (int a = 0; a < MT; ++a)
+#pragma unroll
+                for (int b = 0; b < NTL; ++b)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        dst[(s++) * 32] = hh[a][b][e];
+                        dst[(s++) * 32] = hl[a][b][e];
+                    }
+        }
+        __syncthreads();
+        if (warp == 0) {
+            for (int wsrc = 0; wsrc < KW - 1; ++wsrc) {
+                const float *src = red + (size_t)wsrc * C::NACC * 32 + lane;
+                int s = 0;
+#pragma unroll
+                for (int a = 0; a < MT; ++a)
+#pragma unroll
+                    for (int b = 0; b < NTL; ++b)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            hh[a][b][e] += src[(s++) * 32];
+                            hl[a][b][e] += src[(s++) * 32];
+                        }
+            }
+        }
+    }
+}
+
 // warp 0: S = HH + scale (HL + HL^T) into the shared tile (fragment (a,b,e) -> (row,col)), both triangles
 template <int NT, bool X3>
 __device__ __forceinline__ void small_assemble(float *tile, float (&hh)[NT / 16][NT / 8][4], float (&hl)[NT / 16][NT / 8][4],
@@ -293,16 +439,19 @@ __device__ __forceinline__ void small_assemble(float *tile, float (&hh)[NT / 16]
 // F16 (fp32-grade only): fp16 pieces first; a request with a candidate whose squared norm is not in
 // [2^-12, inf) -- fp16's exponent range was left, or every element underflowed -- is scored again on tf32 pieces by
 // the same CTA (rare: unit-norm or O(1)-norm embeddings never are).
-template <int NT, bool X3, int KW, int U, bool F16 = false>
-__global__ void __launch_bounds__(KW * 32, (NT == 16 ? 32 : 16) / KW)
+// PS > 0 (with F16): the loads of the fp16-piece pass are pipelined through PS shared-memory stages (small_gram_pipe).
+template <int NT, bool X3, int KW, int U, bool F16 = false, int PS = 0>
+__global__ void __launch_bounds__(KW * 32, PS > 0 ? 4 : (NT == 16 ? 32 : 16) / KW)
 score_small_kernel(const ScoreParams p) {
     static_assert(!F16 || X3, "fp16 pieces are the fp32-grade route");
+    static_assert(PS == 0 || F16, "the pipelined loads belong to the fp16-piece pass");
     using C = SmallCfg<NT, X3, KW, U>;
     constexpr int MT = C::MT, NTL = C::NTL, PITCH = C::PITCH;
     extern __shared__ __align__(16) float smem[];
     float *red = smem;                                    // [KW-1][NACC][32]
     float *tile = smem + (size_t)(KW - 1) * C::NACC * 32; // [NT][PITCH]
     float *fl = tile + NT * PITCH + (size_t)(threadIdx.x >> 5) * C::NHH * 32 + (threadIdx.x & 31); // X3: [KW][NHH][32], lane-private
+    float4 *pipe = reinterpret_cast<float4 *>(smem + C::PIPE_OFF_FLOATS); // PS > 0: [KW][PS][U][RPL][32] x 16 B
     __shared__ int redo;
 
     const int r = blockIdx.x;
@@ -319,7 +468,10 @@ score_small_kernel(const ScoreParams p) {
             for (int e = 0; e < 4; ++e) hh[a][b][e] = hl[a][b][e] = 0.f;
 
     if (p.cosine) {
-        small_gram<NT, X3, KW, U, F16>(p, r, red, fl, hh, hl);
+        if (PS > 0)
+            small_gram_pipe<NT, KW, U, (PS > 0 ? PS : 2)>(p, r, red, fl, pipe, hh, hl);
+        else
+            small_gram<NT, X3, KW, U, F16>(p, r, red, fl, hh, hl);
         if (warp == 0) small_assemble<NT, X3>(tile, hh, hl, F16 ? kF16LoScale : 1.0f);
         if (F16) {
             if (warp == 0) {

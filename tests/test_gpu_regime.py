@@ -407,3 +407,32 @@ def test_a_run_of_same_shaped_batches_is_one_launch_with_the_same_bits(lwc, orac
     want = oracle.score_f64(*batches[0], oracle.SIM_COSINE)
     if prec == "fp32":
         assert compare(singles[0], want, batches[0][1]) == 1.0
+
+
+@pytest.mark.parametrize("stages", ["0", "3", "4"])
+def test_cfg3_kernel_load_pipeline_variants(lwc, oracle, stages):
+    """LWC_SMALL_PIPE selects how the 32-candidate fp32-grade kernel (the cfg3 route) feeds its fp16-piece Gram pass:
+    0 = loads into registers, 3 (default) / 4 = cp.async through that many lane-private shared-memory stages.  Same
+    arithmetic in the same order, so the three must agree bit for bit; D values exercise rows shorter than the
+    pipeline, ragged tails and several accumulator flushes."""
+    results = []
+    for D in (3072, 48, 1000, 4400):
+        R, N, M = 500, 32, 4
+        E, V, w = fast_batch(R, N, D, M, seed=900 + D)
+        old = os.environ.get("LWC_SMALL_PIPE")
+        try:
+            os.environ["LWC_SMALL_PIPE"] = stages
+            with lwc.Context(device=0) as c:
+                got = c.score_batch_device(E, V, w)
+            os.environ["LWC_SMALL_PIPE"] = "0"
+            with lwc.Context(device=0) as c:
+                base = c.score_batch_device(E, V, w)
+        finally:
+            if old is None:
+                os.environ.pop("LWC_SMALL_PIPE", None)
+            else:
+                os.environ["LWC_SMALL_PIPE"] = old
+        want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+        assert compare(got, want, V) == 1.0
+        for k in got:
+            assert np.array_equal(got[k], base[k], equal_nan=True), (k, D)
