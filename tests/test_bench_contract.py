@@ -49,10 +49,29 @@ def test_product_arm_refuses_to_run_without_a_gpu():
 
 
 def test_committed_full_line_has_the_contract_keys():
-    d = json.loads(open(os.path.join(ROOT, "profiles", "r1_bench_final.json")).read().strip().splitlines()[-1])
+    d = json.loads(open(os.path.join(ROOT, "profiles", "r2_bench_n1.json")).read().strip().splitlines()[-1])
     assert BASE_KEYS | {"clocks", "roofline", "cpu_baseline"} <= set(d)
     r = d["roofline"]
     assert r["bound"] == "hbm" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9 and r["unit"] == "GB/s"
+    assert abs(r["bytes_per_launch"] - r["bytes_per_step"] * r["steps_per_launch"]) < 1
     assert d["e2e"]["h2d_bytes_per_step"] > 0 and d["e2e"]["d2h_bytes_per_step"] > 0
-    assert d["gpu_launches"] >= d["steps"]
+    assert 0 < d["e2e"]["frac_of_h2d_peak"] <= 1.05 and set(d["e2e"]["other_transports"]) == {"f64", "bf16"}
+    assert 1 <= d["gpu_launches"] <= d["steps"]
     assert d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["sample"]
+    # round 2: parity of the timed output, BASELINE configs[0] literally, the other configs, the host-types leg
+    assert d["parity_sample"]["tolerance_used"] <= 1.0 and d["parity_sample"]["winner_agreement"] == 1.0
+    assert d["cpu_baseline_cfg1"]["threads"] == 1 and d["cpu_baseline_cfg1"]["reps"] >= 1000 and d["gpu_cfg1"]["reps"] >= 1000
+    for k in ("cfg3_strong", "cfg4_fp32", "cfg4_tf32"):
+        assert d["extra"][k]["parity_sample"]["tolerance_used"] <= 1.0, k
+    assert all(rt["check_passed"] for rt in d["extra"]["cfg5_pool"]["routes"])
+    assert set(d["e2e_from_reference_types"]) == {"cfg2_shape", "cfg3_shape", "cfg4_shape"}
+    assert d["host_device_paths_agree"] is True
+
+
+def test_committed_multi_gpu_line_carries_both_pool_routes():
+    d = json.loads(open(os.path.join(ROOT, "profiles", "r2_bench_8gpu.json")).read().strip().splitlines()[-1])
+    assert d["n_gpus"] == 8 and d["scaling"] == "weak" and len(d["per_rank_ms_per_step"]) == 8
+    routes = {rt["route"]: rt for rt in d["extra"]["cfg5_pool"]["routes"]}
+    assert set(routes) == {"nccl_allgather", "fused_p2p_gather"} and all(rt["check_passed"] for rt in routes.values())
+    assert d["extra"]["cfg5_pool"]["rows_total"] == 262144
+    assert d["extra"]["cfg3_strong"]["requests_total"] == 65536
