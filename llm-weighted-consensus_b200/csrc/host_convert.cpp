@@ -30,6 +30,16 @@ static void f64_to_bf16_plain(const double *src, size_t n, uint16_t *dst) {
 #if defined(__x86_64__)
 __attribute__((target("avx2"))) static void f64_to_f32_avx2(const double *src, size_t n, float *dst) {
     size_t i = 0;
+    // A whole embedding row going into a pinned staging arena is written once and next read by the DMA engine:
+    // streaming stores skip the read-for-ownership of every destination line (a third of the pass's memory traffic).
+    if (n >= 256 && (reinterpret_cast<uintptr_t>(dst) & 31u) == 0) {
+        for (; i + 8 <= n; i += 8) {
+            const __m128 a = _mm256_cvtpd_ps(_mm256_loadu_pd(src + i));
+            const __m128 b = _mm256_cvtpd_ps(_mm256_loadu_pd(src + i + 4));
+            _mm256_stream_ps(dst + i, _mm256_set_m128(b, a));
+        }
+        _mm_sfence();
+    }
     for (; i + 8 <= n; i += 8) {
         const __m128 a = _mm256_cvtpd_ps(_mm256_loadu_pd(src + i));
         const __m128 b = _mm256_cvtpd_ps(_mm256_loadu_pd(src + i + 4));
