@@ -442,6 +442,35 @@ def run_b200(args):
     if spread > 0.03 and rank == 0:
         print(f"[bench] WARNING: per-rank step times differ by {100 * spread:.1f} % (> 3 %): {per_rank_ms}", file=sys.stderr, flush=True)
 
+    # ---- the same K steps with one launch per batch (round 1's mode, LWC_LIST_FUSION=0), for comparison in the same line
+    unfused = None
+    if args.launch == "list" and os.environ.get("LWC_LIST_FUSION") != "0":
+        os.environ["LWC_LIST_FUSION"] = "0"
+        ctx_u = lwc_b200.Context(device=local_rank, flags=0 if args.no_overlap else lwc_b200.CTX_INPUTS_RESIDENT)
+        os.environ.pop("LWC_LIST_FUSION", None)
+
+        def list_u(k):
+            return ctx_u.batch_list([desc_dev] * k, [dE[j % n_rot].data_ptr() for j in range(k)], [dV.data_ptr()] * k,
+                                    [dw.data_ptr()] * k, *[[d_outs[j % n_rot][o].data_ptr() for j in range(k)]
+                                                           for o in ("conf", "cw", "agree", "winner", "rank")],
+                                    stream=stream.cuda_stream)
+
+        list_u(args.warmup)()
+        barrier()
+        u0, u1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0 = ctx_u.launch_count()
+        run_u = list_u(args.steps)
+        with torch.cuda.stream(stream):
+            u0.record(stream)
+            run_u()
+            u1.record(stream)
+        barrier()
+        u_ms = max_over_ranks(u0.elapsed_time(u1)) / args.steps
+        unfused = {"ms_per_step": u_ms, "value": world * R / (u_ms * 1e-3), "unit": UNIT, "gpu_launches": int(ctx_u.launch_count() - n0),
+                   "frac": R * synth.algorithmic_bytes_per_request(N, D, M) / (u_ms * 1e-3) / 1e9 / load_peaks()[0],
+                   "what": "the same K steps and buffers with LWC_LIST_FUSION=0: one launch per batch, launches overlapped (round 1's timed loop)"}
+        ctx_u.close()
+
     # ---- end to end: host buffers in, host buffers out, copies inside the timed region
     e2e_steps = max(3, min(args.steps, 20))
     for _ in range(2):
@@ -528,7 +557,7 @@ def run_b200(args):
                                 "programmatic dependent launch: a launch streams its (resident) inputs while the previous one drains")
                                + "; the K timed steps are one lwc_score_batches call: a run of same-shaped batches is scored by one launch per 32 batches"},
         "clocks": sampler.summary(), "per_rank_ms_per_step": per_rank_ms, "per_rank_spread": spread,
-        "host_enqueue_ms": enqueue_ms,
+        "host_enqueue_ms": enqueue_ms, "one_launch_per_batch": unfused,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "wall_ms_per_step": wall_ms / e2e_steps,
                 "api": "lwc_score_batch(LWC_MEM_HOST), pinned host buffers",
