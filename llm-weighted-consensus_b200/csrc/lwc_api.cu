@@ -440,9 +440,89 @@ int launch_convert(lwc_ctx *ctx, int e_type, const void *raw, float *dst, size_t
     return LWC_OK;
 }
 
+// Host-memory call for a batch of a few requests (BASELINE configs[0] is ONE request): latency, not bandwidth.  The
+// chunked pipeline below issues three H2D and five D2H copies over two streams with events between them.  Here V and w
+// are packed into a page-locked block the kernel reads over PCIe, the kernel writes every output into the same block
+// (posted PCIe writes), and E is read where it lies when the caller's buffer is page-locked, else copied once: one
+// launch, one synchronise, at most one copy.  Measured on B200, 1 x 16 x 1536 x 4 from pinned buffers, median wall
+// clock around the call: 46-50 us chunked pipeline, 41.6 all-HBM packed (mode 0), 32.1 outputs over PCIe (1),
+// 22.8-24.6 V/w too (2), 19.2 E in place (4, default); the CPU port takes 48.5 us (profiles/r2_cfg1_latency.jsonl).
+constexpr size_t kSmallCallBytes = (size_t)256 << 10;
+
+int score_host_small(lwc_ctx *ctx, const lwc_batch_desc &d, const Plan &pl, const float *E, const float *V, const float *w,
+                     float *conf, float *cw, float *agree, int32_t *winner, int32_t *rank) {
+    const bool cosine = d.similarity == LWC_SIM_COSINE;
+    auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    const size_t R = (size_t)d.R, N = (size_t)d.N, M = (size_t)d.M;
+    const size_t e_b = cosine ? R * N * d.D * 4 : 0, v_b = R * M * N * 4, w_b = (d.w_per_request ? R : 1) * M * 4;
+    const size_t o_e = 0, o_v = up(e_b), o_w = o_v + up(v_b), o_out = o_w + up(w_b);
+    const size_t c_b = R * N * 4, a_b = R * M * 4, wi_b = R * 4;
+    const size_t o_conf = o_out, o_cw = o_conf + up(c_b), o_ag = o_cw + up(c_b), o_win = o_ag + up(a_b), o_rank = o_win + up(wi_b);
+    const size_t total = o_rank + up(c_b);
+    if (total > ctx->small_cap) {
+        if (ctx->small_dev) CUDA_TRY(ctx, cudaFree(ctx->small_dev));
+        if (ctx->small_pin) CUDA_TRY(ctx, cudaFreeHost(ctx->small_pin));
+        ctx->small_dev = ctx->small_pin = nullptr, ctx->small_cap = 0;
+        const size_t want = total * 2 + 4096;
+        CUDA_TRY(ctx, cudaMalloc(&ctx->small_dev, want));
+        CUDA_TRY(ctx, cudaHostAlloc(&ctx->small_pin, want, cudaHostAllocDefault));
+        ctx->small_cap = want;
+    }
+    char *dev = static_cast<char *>(ctx->small_dev), *pin = static_cast<char *>(ctx->small_pin);
+    cudaStream_t st = ctx->stream;
+    // small_zero_copy: 0 = every buffer in HBM (3 copies); 1 = outputs written into the pinned block; 2 = V and w read
+    // from it too (E copied); 3 = E through the block as well; 4 = E read in place when page-locked, else as 2.
+    const int zc = ctx->small_zero_copy;
+    char *in_e = zc >= 3 ? pin : dev, *in_vw = zc >= 2 ? pin : dev, *outb = zc >= 1 ? pin : dev;
+    const float *e_direct = nullptr; // mode 4: the caller's E is page-locked -- the kernel reads it where it lies
+    if (cosine && zc >= 4) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, E) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+            e_direct = static_cast<const float *>(at.devicePointer);
+        else
+            in_e = dev;
+        (void)cudaGetLastError();
+    }
+    if (cosine && !e_direct) {
+        if (in_e == pin) memcpy(pin + o_e, E, e_b);
+        else CUDA_TRY(ctx, cudaMemcpyAsync(dev + o_e, E, e_b, cudaMemcpyHostToDevice, st));
+    }
+    if (M > 0) {
+        memcpy(pin + o_v, V, v_b);
+        memcpy(pin + o_w, w, w_b);
+        if (zc < 2) CUDA_TRY(ctx, cudaMemcpyAsync(dev + o_v, pin + o_v, o_out - o_v, cudaMemcpyHostToDevice, st));
+    }
+    lwc::ScoreParams p;
+    p.E = e_direct ? e_direct : reinterpret_cast<const float *>(in_e + o_e);
+    p.V = reinterpret_cast<const float *>(in_vw + o_v);
+    p.w = reinterpret_cast<const float *>(in_vw + o_w);
+    p.conf = conf ? reinterpret_cast<float *>(outb + o_conf) : nullptr;
+    p.cw = cw ? reinterpret_cast<float *>(outb + o_cw) : nullptr;
+    p.agree = agree ? reinterpret_cast<float *>(outb + o_ag) : nullptr;
+    p.winner = winner ? reinterpret_cast<int32_t *>(outb + o_win) : nullptr;
+    p.rank = rank ? reinterpret_cast<int32_t *>(outb + o_rank) : nullptr;
+    p.R = d.R, p.N = d.N, p.D = d.D, p.M = d.M;
+    p.w_per_request = d.w_per_request;
+    p.cosine = cosine ? 1 : 0;
+    p.inputs_resident = 0;
+    int rc = launch_plan(ctx, pl, p, st);
+    if (rc) return rc;
+    if (zc < 1) CUDA_TRY(ctx, cudaMemcpyAsync(pin + o_out, dev + o_out, total - o_out, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    if (conf) memcpy(conf, pin + o_conf, c_b);
+    if (cw) memcpy(cw, pin + o_cw, c_b);
+    if (agree && M > 0) memcpy(agree, pin + o_ag, a_b);
+    if (winner) memcpy(winner, pin + o_win, wi_b);
+    if (rank) memcpy(rank, pin + o_rank, c_b);
+    return LWC_OK;
+}
+
 int score_host(lwc_ctx *ctx, const lwc_batch_desc &d, const Plan &pl, int e_type, const void *E, const float *V, const float *w,
                float *conf, float *cw, float *agree, int32_t *winner, int32_t *rank) {
     const bool cosine = d.similarity == LWC_SIM_COSINE;
+    if (e_type == LWC_ELEM_F32 && ctx->chunk_requests <= 0 &&
+        (size_t)d.R * ((cosine ? (size_t)d.N * d.D * 4 : 0) + (size_t)d.M * d.N * 4 + (size_t)d.N * 16 + (size_t)d.M * 8 + 1024) <= kSmallCallBytes)
+        return score_host_small(ctx, d, pl, static_cast<const float *>(E), V, w, conf, cw, agree, winner, rank);
     const size_t e_req = cosine ? (size_t)d.N * d.D * sizeof(float) : 0;         // fp32 tile the kernels read
     const size_t e_raw = cosine ? (size_t)d.N * d.D * elem_size(e_type) : 0;     // what crosses PCIe
     const bool typed = e_type != LWC_ELEM_F32;
@@ -598,6 +678,7 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     if (const char *s = getenv("LWC_TC_X3")) ctx->tc_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_X3")) ctx->small_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_PIPE")) ctx->small_pipe = atoi(s);
+    if (const char *s = getenv("LWC_SMALL_ZERO_COPY")) ctx->small_zero_copy = atoi(s);
     if (const char *s = getenv("LWC_TC_STAGES")) ctx->tc_stages = atoi(s);
     if (ctx->stream_ncw != 0 && ctx->stream_ncw != 4 && ctx->stream_ncw != 8 && ctx->stream_ncw != 12) ctx->stream_ncw = 0;
     if (ctx->stream_kc < 0 || ctx->stream_kc % 16) ctx->stream_kc = 0;
@@ -629,6 +710,8 @@ void lwc_ctx_destroy(lwc_ctx *ctx) {
             if (q) cudaIpcCloseMemHandle(q);
     if (ctx->p2p_dev) cudaFree(ctx->p2p_dev);
     if (ctx->typed_buf) cudaFree(ctx->typed_buf);
+    if (ctx->small_dev) cudaFree(ctx->small_dev);
+    if (ctx->small_pin) cudaFreeHost(ctx->small_pin);
     if (ctx->tc_flags) cudaFree(ctx->tc_flags);
     for (auto &b : ctx->table_buf)
         if (b) cudaFree(b);

@@ -66,6 +66,9 @@ struct lwc_ctx {
     int no_list_fusion = 0;    // LWC_LIST_FUSION=0: lwc_score_batches launches batch by batch even where one launch could take a run
     int weights_in_flight = 0; // lwc_table_weights(LWC_MEM_DEVICE) has queued a kernel that writes a caller's `w`: the next
                                // lwc_score_batch must not let its input reads run ahead of the stream (LWC_CTX_INPUTS_RESIDENT)
+    void *small_dev = nullptr, *small_pin = nullptr; // device block + pinned bounce of the few-request host path
+    size_t small_cap = 0;
+    int small_zero_copy = 4; // LWC_SMALL_ZERO_COPY: which of the few-request path's buffers the kernel reaches over PCIe (0 = none)
     void *typed_buf = nullptr; // fp32 copy of device-resident f64 / bf16 embeddings (lwc_score_batch_typed)
     size_t typed_cap = 0;
     void *tc_flags = nullptr;  // per-request fix-up marks of the fp16-piece tcgen05 route (score_tc16.cuh)

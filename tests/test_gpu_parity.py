@@ -486,3 +486,40 @@ def test_shape_extremes(ctx, lwc, oracle, case):
     if N == 1 and M > 0:
         scored = got["winner"] >= 0
         assert np.all(got["conf"][scored, 0] == 1.0)
+
+
+@pytest.mark.parametrize("shape", [(1, 16, 1536, 4), (2, 16, 1536, 4), (40, 16, 96, 4), (1, 32, 1536, 8), (2, 128, 256, 3), (5, 9, 40, 0)],
+                         ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+@pytest.mark.parametrize("sim", ["cosine", "identity"])
+def test_few_request_host_call_equals_the_chunked_pipeline(lwc, oracle, shape, sim):
+    """A host-memory call of a few requests takes the packed low-latency path (lwc_api.cu, score_host_small: the kernel
+    reads V, w -- and E, when it is page-locked -- over PCIe and writes its outputs there); the same call with a chunk
+    size set takes the two-stream chunked pipeline.  Same kernels, same bits, whichever way the bytes travel."""
+    from lwc_b200 import synth
+
+    R, N, D, M = shape
+    E, V, w, _ = synth.make_batch(R, N, D, max(M, 1), seed=17)
+    if M == 0:
+        V, w = V[:, :0], w[:, :0]
+    similarity = lwc.SIM_COSINE if sim == "cosine" else lwc.SIM_IDENTITY
+    packed, chunked = lwc.Context(device=0), lwc.Context(device=0, chunk_requests=2)
+    pinned = lwc.HostBuffer(packed, E.shape, np.float32)
+    try:
+        pinned.array[...] = E
+        a = packed.score_batch(E, V, w, similarity=similarity)             # pageable E: one H2D copy
+        p = packed.score_batch(pinned.array, V, w, similarity=similarity)  # page-locked E: read in place
+        b = chunked.score_batch(E, V, w, similarity=similarity)
+        c = packed.score_batch(pinned.array, V, w[0], similarity=similarity) if M else None  # shared weight vector
+        d = chunked.score_batch(E, V, w[0], similarity=similarity) if M else None
+    finally:
+        pinned.free()
+        packed.close()
+        chunked.close()
+    for k in a:
+        assert np.array_equal(a[k], b[k], equal_nan=True), k
+        assert np.array_equal(p[k], b[k], equal_nan=True), k
+        if c is not None:
+            assert np.array_equal(c[k], d[k], equal_nan=True), k
+    if sim == "cosine":
+        want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+        assert compare(a, want, V) == 1.0
