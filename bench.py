@@ -623,6 +623,9 @@ def host_types_leg(device, with_cpu=True):
                 out[name] = {"unavailable": f"tools/e2e_host exited {run.returncode}: {run.stderr[-300:]}"}
                 continue
             out[name] = json.loads(lines[-1])
+            if out[name].get("convert_only_requests_per_s"):
+                # the bare f64 -> fp32 pass over the same heap rows by the same threads: what "host-bound" means here
+                out[name]["frac_of_convert_only"] = out[name]["value"] / out[name]["convert_only_requests_per_s"]
             if with_cpu:
                 import oracle
                 from lwc_b200 import synth
