@@ -76,6 +76,7 @@ struct Plan {
     Route route = ROUTE_INVALID;
     int np = 0;      // padded pool size
     bool x3 = true;  // small route: compensated 3xTF32
+    bool pair = false; // tcgen05 fp32-grade route: two requests of <= 64 candidates per tile
     const char *name = "";
 };
 
@@ -108,6 +109,9 @@ Plan plan_for(const lwc_batch_desc &d, const void *E) {
         pl.np = 128;
         pl.x3 = (d.precision == LWC_PREC_FP32 || d.precision == LWC_PREC_TF32X3);
         pl.name = pl.x3 ? "tc128_f16x2" : "tc128_tf32"; // LWC_TC_X3=tf32 runs the fp32-grade route on tf32 pieces ("tc128_tf32x3")
+        // pools of at most 64 candidates: two requests per 128-row tile (score_tc16.cuh, PAIR); LWC_TC_PAIR=0 keeps one
+        pl.pair = d.N <= 64;
+        if (pl.pair) pl.name = pl.x3 ? "tc64x2_f16x2" : "tc64x2_tf32";
         return pl;
     }
     pl.route = ROUTE_GENERIC;
@@ -195,6 +199,20 @@ cudaError_t launch_small(const lwc::ScoreParams &p, cudaStream_t st, int kw, int
 
 // E viewed as a rank-4 fp32 tensor {32 (k_in), N (row), D/32 (k_out), R}: one box {32, 128, ko, 1} lands as
 // ko K-major SWIZZLE_128B operand slabs of [128 rows x 128 B] (score_tc.cuh).
+// Pools of at most 64 candidates, two requests to a tile: the view {32 (k_in), N (row), R, D/32 (k_out)}; one box
+// {32, 64, 2, ko} lands as ko slabs whose rows 0..63 are request 2g's and 64..127 request 2g+1's (zero-filled past N and R).
+bool make_tensor_map_tc_pair(CUtensorMap *tm, const float *E, int R, int N, int D, int ko) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) return false;
+    cuuint64_t dims[4] = {32, (cuuint64_t)N, (cuuint64_t)R, (cuuint64_t)(D / 32)};
+    cuuint64_t strides[3] = {(cuuint64_t)D * 4, (cuuint64_t)N * D * 4, 128};
+    cuuint32_t box[4] = {32, 64, 2, (cuuint32_t)ko};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    return fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float *>(E), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 bool make_tensor_map_tc(CUtensorMap *tm, const float *E, int R, int N, int D, int ko) {
     EncodeTiledFn fn = encode_tiled_fn();
     if (!fn) return false;
@@ -207,7 +225,7 @@ bool make_tensor_map_tc(CUtensorMap *tm, const float *E, int R, int N, int D, in
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-template <bool X3>
+template <bool X3, bool PAIR = false>
 cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st, const int *fix_flags = nullptr) {
     lwc::TcGeom geo;
     geo.ko = ctx->tc_ko > 0 ? ctx->tc_ko : (X3 ? 2 : 4); // 64 KB per stage either way (profiles/r1_tma_probe2.txt)
@@ -219,16 +237,18 @@ cudaError_t launch_tc(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st, 
     if (lwc::tc_smem_bytes(geo.ko, geo.stages, X3) > (size_t)ctx->max_smem_optin) return cudaErrorInvalidConfiguration;
     static std::atomic<bool> configured[64]; // zero-initialised; set once per device (contexts on other threads may race here)
     if (!configured[ctx->device & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(lwc::score_tc_kernel<X3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_tc_kernel<X3, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              ctx->max_smem_optin);
         if (e != cudaSuccess) return e;
         configured[ctx->device & 63] = true;
     }
     CUtensorMap tm;
     // fp32-grade route: one box per slab (the slabs of a stage are interleaved with their remainder slabs)
-    if (!make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, X3 ? 1 : geo.ko)) return cudaErrorInvalidValue;
-    const int grid = p.R < ctx->sm_count ? p.R : ctx->sm_count;
-    lwc::score_tc_kernel<X3><<<grid, X3 ? lwc::kTcThreadsX3 : lwc::kTcThreads, lwc::tc_smem_bytes(geo.ko, geo.stages, X3), st>>>(
+    if (!(PAIR ? make_tensor_map_tc_pair(&tm, p.E, p.R, p.N, p.D, geo.ko) : make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, X3 ? 1 : geo.ko)))
+        return cudaErrorInvalidValue;
+    const int ntiles = PAIR ? (p.R + 1) / 2 : p.R;
+    const int grid = ntiles < ctx->sm_count ? ntiles : ctx->sm_count;
+    lwc::score_tc_kernel<X3, PAIR><<<grid, X3 ? lwc::kTcThreadsX3 : lwc::kTcThreads, lwc::tc_smem_bytes(geo.ko, geo.stages, X3), st>>>(
         tm, p, geo, fix_flags);
     return cudaGetLastError();
 }
@@ -237,7 +257,7 @@ cudaError_t ensure_fix_flags(lwc_ctx *ctx, int R);
 
 // fp32-grade route at kind::f16 rate (score_tc16.cuh) + its fix-up pass: the requests whose norms fall outside
 // what fp16 pieces represent exactly enough are marked by the first kernel and re-scored by the tf32 kernel.
-cudaError_t launch_tc16(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
+cudaError_t launch_tc16(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st, bool pair) {
     lwc::TcGeom geo;
     geo.ko = 2;
     geo.stages = lwc::kT16MaxStages;
@@ -246,7 +266,9 @@ cudaError_t launch_tc16(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st
     if (lwc::tc16_smem_bytes(geo.stages) > (size_t)ctx->max_smem_optin) return cudaErrorInvalidConfiguration;
     static std::atomic<bool> configured[64];
     if (!configured[ctx->device & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(lwc::score_tc16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_tc16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(lwc::score_tc16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
         if (e != cudaSuccess) return e;
         configured[ctx->device & 63] = true;
     }
@@ -255,9 +277,14 @@ cudaError_t launch_tc16(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st
         if (e != cudaSuccess) return e;
     }
     CUtensorMap tm;
-    if (!make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, 2)) return cudaErrorInvalidValue;
-    const int grid = p.R < ctx->sm_count ? p.R : ctx->sm_count;
-    lwc::score_tc16_kernel<<<grid, lwc::kT16Threads, lwc::tc16_smem_bytes(geo.stages), st>>>(tm, p, geo, static_cast<int *>(ctx->tc_flags));
+    if (!(pair ? make_tensor_map_tc_pair(&tm, p.E, p.R, p.N, p.D, 2) : make_tensor_map_tc(&tm, p.E, p.R, p.N, p.D, 2)))
+        return cudaErrorInvalidValue;
+    const int ntiles = pair ? (p.R + 1) / 2 : p.R;
+    const int grid = ntiles < ctx->sm_count ? ntiles : ctx->sm_count;
+    if (pair)
+        lwc::score_tc16_kernel<true><<<grid, lwc::kT16Threads, lwc::tc16_smem_bytes(geo.stages), st>>>(tm, p, geo, static_cast<int *>(ctx->tc_flags));
+    else
+        lwc::score_tc16_kernel<false><<<grid, lwc::kT16Threads, lwc::tc16_smem_bytes(geo.stages), st>>>(tm, p, geo, static_cast<int *>(ctx->tc_flags));
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     ctx->launches++;
@@ -383,7 +410,8 @@ int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStr
     cudaError_t e = cudaSuccess;
     const SmallRoute sr = small_route(ctx, pl);
     if (pl.route == ROUTE_TC) {
-        e = !pl.x3 ? launch_tc<false>(ctx, p, st) : (ctx->tc_x3_tf32 ? launch_tc<true>(ctx, p, st) : launch_tc16(ctx, p, st));
+        const bool pair = pl.pair && !ctx->tc_no_pair;
+        e = !pl.x3 ? (pair ? launch_tc<false, true>(ctx, p, st) : launch_tc<false>(ctx, p, st)) : (ctx->tc_x3_tf32 ? launch_tc<true>(ctx, p, st) : launch_tc16(ctx, p, st, pair));
     } else if (pl.route == ROUTE_SMALL && sr.stream) {
         if (pl.np == 16)
             e = pl.x3 ? launch_stream<16, true>(ctx, p, st) : launch_stream<16, false>(ctx, p, st);
@@ -676,6 +704,7 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     if (const char *s = getenv("LWC_LIST_FUSION")) ctx->no_list_fusion = atoi(s) == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_TC_KO")) ctx->tc_ko = atoi(s);
     if (const char *s = getenv("LWC_TC_X3")) ctx->tc_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
+    if (const char *s = getenv("LWC_TC_PAIR")) ctx->tc_no_pair = atoi(s) == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_X3")) ctx->small_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_PIPE")) ctx->small_pipe = atoi(s);
     if (const char *s = getenv("LWC_SMALL_ZERO_COPY")) ctx->small_zero_copy = atoi(s);
@@ -786,6 +815,7 @@ const char *lwc_kernel_for(const lwc_ctx *ctx, const lwc_batch_desc *desc) {
     // alignment is unknown here: assume the documented 16-byte alignment of E
     const Plan pl = plan_for(*desc, nullptr);
     if (ctx && ctx->tc_x3_tf32 && pl.route == ROUTE_TC && pl.x3) return "tc128_tf32x3";
+    if (ctx && ctx->tc_no_pair && pl.pair) return pl.x3 ? "tc128_f16x2" : "tc128_tf32";
     if (ctx && pl.route == ROUTE_SMALL && pl.x3) {
         const SmallRoute sr = small_route(ctx, pl);
         if (sr.f16) return pl.np == 16 ? "small16_f16x2" : "small32_f16x2";

@@ -144,9 +144,14 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 // named barrier over the 128 epilogue threads only
 __device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-template <bool X3>
+// PAIR (TF32 route only): pools of at most 64 candidates ride two to a tile -- the tensor map is the view
+// {32, N, R, D/32}, one box {32, 64, 2, KO} lands requests 2g and 2g+1 as rows 0..63 and 64..127 of the same slabs, the
+// MMA is unchanged (its off-diagonal 64 x 64 blocks are cross products nobody reads) and every per-request reduction
+// of the epilogue runs over the two warps that own the request's rows (see score_tc16.cuh for the fp32-grade twin).
+template <bool X3, bool PAIR = false>
 __global__ void __launch_bounds__(X3 ? kTcThreadsX3 : kTcThreads, 1)
 score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, const TcGeom geo, const int *__restrict__ fix_flags) {
+    static_assert(!(X3 && PAIR), "the fp32-grade pair route is score_tc16_kernel<true>");
     // fix_flags != nullptr: fix-up pass behind score_tc16_kernel (score_tc16.cuh) -- only the requests it marked are
     // scored here; every role skips the others, so the pipelines stay in step
     extern __shared__ __align__(1024) unsigned char smem_tc[];
@@ -172,8 +177,9 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int N = p.N, D = p.D, M = p.M;
-    const int r_begin = (int)(((long long)blockIdx.x * p.R) / gridDim.x);
-    const int r_end = (int)(((long long)(blockIdx.x + 1) * p.R) / gridDim.x);
+    const int ntiles = PAIR ? (p.R + 1) >> 1 : p.R; // a tile holds one request, or a pair of them
+    const int r_begin = (int)(((long long)blockIdx.x * ntiles) / gridDim.x);
+    const int r_end = (int)(((long long)(blockIdx.x + 1) * ntiles) / gridDim.x);
     const int nreq = r_end - r_begin;
     const int nslab = D >> 5;                  // 32-column operand slabs per request (D % 32 == 0)
     const int spr = (nslab + KO - 1) / KO;     // stages per request
@@ -235,7 +241,10 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                                         full0 + 8 * slot);
                     } else {
                         mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)(KO * kTcSlabBytes)); // OOB zero-fill counts too
-                        tma_load_4d(ring_u32 + slot * stageb, &tmE, 0, 0, s * KO, r_begin + q, full0 + 8 * slot);
+                        if (PAIR)
+                            tma_load_4d(ring_u32 + slot * stageb, &tmE, 0, 0, 2 * (r_begin + q), s * KO, full0 + 8 * slot);
+                        else
+                            tma_load_4d(ring_u32 + slot * stageb, &tmE, 0, 0, s * KO, r_begin + q, full0 + 8 * slot);
                     }
                     if (++slot == S) {
                         slot = 0;
@@ -344,13 +353,19 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
         // ===================== epilogue =====================
         const int i = threadIdx.x - 128;   // row of S owned by this thread == TMEM lane
         const int ew = warp - 4;           // TMEM lane quarter this warp may access
-        const bool act = i < N;
+        constexpr int NCH = PAIR ? 2 : 4;  // 32-column chunks of a request's accumulator columns
+        const int hq = PAIR ? (ew >> 1) : 0;   // which request of the tile this row belongs to
+        const int ii = PAIR ? (i & 63) : i;    // candidate index
+        const int cbase = hq * 64;             // first accumulator column / row of that request
+        const int w0 = PAIR ? 2 * hq : 0;      // first of the epilogue warps that own the request
         const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
         uint32_t tile = 0;
         const int nchunk = X3 ? (spr + cst - 1) / cst : 1;
         for (int q = 0; q < nreq; ++q) {
-            const int r = r_begin + q;
-            if (fix_flags && !__ldg(fix_flags + r)) continue;
+            const int r = PAIR ? 2 * (r_begin + q) + hq : r_begin + q;
+            if (!PAIR && fix_flags && !__ldg(fix_flags + r)) continue;
+            const bool exists = r < p.R; // an odd batch ends on a half-empty tile
+            const bool act = exists && ii < N;
             const float *Vr = p.V + (size_t)r * M * N;
             const float *wr = p.w + (p.w_per_request ? (size_t)r * M : 0);
             // t_i = sum_m w_m V_mi (client.rs:410-415): independent of E, overlaps the MMAs.  Eight voters' loads are
@@ -362,10 +377,10 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
                     const int m = m0 + u;
-                    const bool ok = m < M;
+                    const bool ok = m < M && exists;
                     v0[u] = ok ? __ldg(Vr + (size_t)m * N) : __int_as_float(0x7fc00000);
                     wv[u] = ok ? __ldg(wr + m) : 0.f;
-                    vi[u] = (ok && act) ? __ldg(Vr + (size_t)m * N + i) : 0.f;
+                    vi[u] = (ok && act) ? __ldg(Vr + (size_t)m * N + ii) : 0.f;
                 }
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
@@ -467,10 +482,10 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                 u_s[i] = t * rn;
                 epi_sync();
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    tmem_ld32(row_addr + (uint32_t)(c * 32), v);
+                for (int c = 0; c < NCH; ++c) { // the request's own columns
+                    tmem_ld32(row_addr + (uint32_t)(cbase + c * 32), v);
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) acc = fmaf(u_s[c * 32 + e], v[e], acc);
+                    for (int e = 0; e < 32; ++e) acc = fmaf(u_s[cbase + c * 32 + e], v[e], acc);
                 }
                 // accumulator fully read: hand it back to the MMA warp
                 tc_fence_before();
@@ -482,17 +497,17 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
             float ws = warp_sum(c);
             if (lane == 0) part[ew] = ws;
             epi_sync();
-            const float sum = (part[0] + part[1]) + (part[2] + part[3]);
+            const float sum = PAIR ? part[w0] + part[w0 + 1] : (part[0] + part[1]) + (part[2] + part[3]);
             const bool positive = sum > 0.f;
             const float cf = (positive && act) ? c / sum : 0.f;
             cf_s[i] = cf;
             if (act) {
-                if (p.cw) p.cw[(size_t)r * N + i] = c;
-                if (p.conf) p.conf[(size_t)r * N + i] = cf;
+                if (p.cw) p.cw[(size_t)r * N + ii] = c;
+                if (p.conf) p.conf[(size_t)r * N + ii] = cf;
             }
             if (p.winner) {
                 float bv = act ? cf : -1.f;
-                int bi = act ? i : 0x7fffffff;
+                int bi = act ? ii : 0x7fffffff;
                 warp_argmax(bv, bi);
                 if (lane == 0) {
                     part[4 + ew] = bv;
@@ -500,45 +515,46 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, co
                 }
             }
             epi_sync();
-            if (p.winner && i == 0) {
-                float best = part[4];
-                int besti = ipart[0];
+            if (p.winner && ii == 0 && exists) {
+                float best = part[4 + w0];
+                int besti = ipart[w0];
 #pragma unroll
-                for (int k = 1; k < 4; ++k)
-                    if (part[4 + k] > best || (part[4 + k] == best && ipart[k] < besti)) {
-                        best = part[4 + k];
-                        besti = ipart[k];
+                for (int k = 1; k < (PAIR ? 2 : 4); ++k)
+                    if (part[4 + w0 + k] > best || (part[4 + w0 + k] == best && ipart[w0 + k] < besti)) {
+                        best = part[4 + w0 + k];
+                        besti = ipart[w0 + k];
                     }
                 p.winner[r] = positive ? besti : -1;
             }
             if (p.rank && act) {
                 int pos = 0;
                 for (int j = 0; j < N; ++j) {
-                    const float cj = cf_s[j];
-                    pos += (cj > cf || (cj == cf && j < i)) ? 1 : 0;
+                    const float cj = cf_s[cbase + j];
+                    pos += (cj > cf || (cj == cf && j < ii)) ? 1 : 0;
                 }
-                p.rank[(size_t)r * N + pos] = i;
+                p.rank[(size_t)r * N + pos] = ii;
             }
-            if (p.agree) {
-                for (int m0 = ew; m0 < M; m0 += 16) { // one warp per voter, four voters' loads in flight
+            if (p.agree && exists) {
+                constexpr int NW = PAIR ? 2 : 4; // warps sharing this request's voters
+                for (int m0 = ew - w0; m0 < M; m0 += 4 * NW) { // one warp per voter, four voters' loads in flight
                     float v0[4], s4[4];
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        const int m = m0 + 4 * u;
+                        const int m = m0 + NW * u;
                         v0[u] = m < M ? __ldg(Vr + (size_t)m * N) : 0.f;
                         s4[u] = 0.f;
                     }
                     for (int j = lane; j < N; j += 32) {
-                        const float cj = cf_s[j];
+                        const float cj = cf_s[cbase + j];
 #pragma unroll
                         for (int u = 0; u < 4; ++u) {
-                            const int m = m0 + 4 * u;
+                            const int m = m0 + NW * u;
                             if (m < M) s4[u] = fmaf(cj, __ldg(Vr + (size_t)m * N + j), s4[u]);
                         }
                     }
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        const int m = m0 + 4 * u;
+                        const int m = m0 + NW * u;
                         if (m >= M) break;
                         const float a = isnan(v0[u]) ? __int_as_float(0x7fc00000) : warp_sum(s4[u]);
                         if (lane == 0) p.agree[(size_t)r * M + m] = a;

@@ -97,6 +97,12 @@ __device__ __forceinline__ void split_f16x8(const float4 &a, const float4 &b, ui
     l = make_uint4(lp[0], lp[1], lp[2], lp[3]);
 }
 
+// PAIR: pools of at most 64 candidates ride two to a tile.  The tensor map is the rank-4 view {32, N, R, D/32} and one
+// box {32, 64, 2, 2} lands requests 2g and 2g+1 as rows 0..63 and 64..127 of the same two slabs; the MMA is unchanged
+// (its off-diagonal 64 x 64 blocks are the two requests' cross products and are never read), every epilogue thread
+// works on its own request's half of the accumulator columns, and each per-request reduction runs over the two warps
+// that own that half.  A 64-candidate pool then costs the shared-memory pipe half of what it costs alone in a tile.
+template <bool PAIR>
 __global__ void __launch_bounds__(kT16Threads, 1)
 score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, const TcGeom geo, int *__restrict__ fix_flags) {
     extern __shared__ __align__(1024) unsigned char smem_t16[];
@@ -115,8 +121,9 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int N = p.N, D = p.D, M = p.M;
-    const int r_begin = (int)(((long long)blockIdx.x * p.R) / gridDim.x);
-    const int r_end = (int)(((long long)(blockIdx.x + 1) * p.R) / gridDim.x);
+    const int ntiles = PAIR ? (p.R + 1) >> 1 : p.R; // a tile holds one request, or a pair of them
+    const int r_begin = (int)(((long long)blockIdx.x * ntiles) / gridDim.x);
+    const int r_end = (int)(((long long)(blockIdx.x + 1) * ntiles) / gridDim.x);
     const int nreq = r_end - r_begin;
     const int upr = (D + 63) >> 6; // units per request (D % 32 == 0; a last half unit arrives zero-filled)
 
@@ -166,7 +173,10 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
                 for (int u = 0; u < upr; ++u) {
                     mbar_wait_backoff(empty0 + 8 * slot, phase ^ 1u, kT16BackoffP);
                     mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)kT16UnitBytes); // OOB zero-fill counts too
-                    tma_load_4d(ring_u32 + slot * kT16UnitBytes, &tmE, 0, 0, 2 * u, r_begin + q, full0 + 8 * slot);
+                    if (PAIR)
+                        tma_load_4d(ring_u32 + slot * kT16UnitBytes, &tmE, 0, 0, 2 * (r_begin + q), 2 * u, full0 + 8 * slot);
+                    else
+                        tma_load_4d(ring_u32 + slot * kT16UnitBytes, &tmE, 0, 0, 2 * u, r_begin + q, full0 + 8 * slot);
                     if (++slot == S) {
                         slot = 0;
                         phase ^= 1u;
@@ -226,6 +236,12 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
         const uint32_t in1 = (uint32_t)(r * 128 + (((2 * pq + 1) ^ r) << 4)); // columns 8pq+4 .. 8pq+7
         const uint32_t out0 = (uint32_t)(r * 128 + ((pq ^ r) << 4));          // fp16 chunk of slab 0's columns
         const uint32_t out1 = (uint32_t)(r * 128 + (((4 + pq) ^ r) << 4));    // fp16 chunk of slab 1's columns
+        // rows past the pool arrive zero-filled, and zero fp32 bits already are zero h and l pieces: their atoms are left alone
+        const int natoms = (N + 7) >> 3;
+        constexpr int kAtomMask = PAIR ? 7 : 15;
+        bool on[16 / NTW];
+#pragma unroll
+        for (int k = 0; k < 16 / NTW; ++k) on[k] = ((tw + k * NTW) & kAtomMask) < natoms;
         int slot = 0;
         uint32_t phase = 0;
         for (int q = 0; q < nreq; ++q)
@@ -238,6 +254,7 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
                 float4 x[16 / NTW][4];
 #pragma unroll
                 for (int k = 0; k < 16 / NTW; ++k) {
+                    if (!on[k]) continue;
                     const uint32_t a0 = base + (uint32_t)(tw + k * NTW) * 1024u, a1 = a0 + (uint32_t)kTcSlabBytes;
                     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x[k][0].x), "=f"(x[k][0].y), "=f"(x[k][0].z), "=f"(x[k][0].w) : "r"(a0 + in0));
                     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x[k][1].x), "=f"(x[k][1].y), "=f"(x[k][1].z), "=f"(x[k][1].w) : "r"(a0 + in1));
@@ -247,6 +264,7 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
                 __syncwarp(); // every lane has read its atoms before any lane overwrites them
 #pragma unroll
                 for (int k = 0; k < 16 / NTW; ++k) {
+                    if (!on[k]) continue;
                     const uint32_t a0 = base + (uint32_t)(tw + k * NTW) * 1024u, a1 = a0 + (uint32_t)kTcSlabBytes;
                     uint4 h0, l0, h1, l1;
                     split_f16x8(x[k][0], x[k][1], h0, l0);
@@ -267,14 +285,20 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
             }
     } else if (warp >= 4 && warp < 8) {
         // ===================== epilogue =====================
-        const int i = threadIdx.x - 128;
+        const int i = threadIdx.x - 128; // accumulator row
         const int ew = warp - 4;
-        const bool act = i < N;
+        constexpr int NCH = PAIR ? 2 : 4;              // 32-column chunks of a request's accumulator columns
+        const int hq = PAIR ? (ew >> 1) : 0;           // which request of the tile this row belongs to
+        const int ii = PAIR ? (i & 63) : i;            // candidate index
+        const int cbase = hq * 64;                     // first accumulator column / row of that request
+        const int w0 = PAIR ? 2 * hq : 0;              // first of the epilogue warps that own the request
         const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
         uint32_t tile = 0;
         const int nchunk = (upr + kT16ChunkUnits - 1) / kT16ChunkUnits;
         for (int q = 0; q < nreq; ++q) {
-            const int r = r_begin + q;
+            const int r = PAIR ? 2 * (r_begin + q) + hq : r_begin + q;
+            const bool exists = r < p.R; // an odd batch ends on a half-empty tile
+            const bool act = exists && ii < N;
             const float *Vr = p.V + (size_t)r * M * N;
             const float *wr = p.w + (p.w_per_request ? (size_t)r * M : 0);
             // t_i = sum_m w_m V_mi (client.rs:410-415), eight voters' loads in flight at a time
@@ -284,10 +308,10 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
                     const int m = m0 + u;
-                    const bool ok = m < M;
+                    const bool ok = m < M && exists;
                     v0[u] = ok ? __ldg(Vr + (size_t)m * N) : __int_as_float(0x7fc00000);
                     wv[u] = ok ? __ldg(wr + m) : 0.f;
-                    vi[u] = (ok && act) ? __ldg(Vr + (size_t)m * N + i) : 0.f;
+                    vi[u] = (ok && act) ? __ldg(Vr + (size_t)m * N + ii) : 0.f;
                 }
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
@@ -297,9 +321,9 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
                 }
             }
             float v[32];
-            float row[128];
+            float row[NCH * 32]; // this candidate's row of S over its own request's columns
 #pragma unroll
-            for (int e = 0; e < 128; ++e) row[e] = 0.f;
+            for (int e = 0; e < NCH * 32; ++e) row[e] = 0.f;
             uint32_t z[32];
 #pragma unroll
             for (int e = 0; e < 32; ++e) z[e] = 0u;
@@ -310,11 +334,14 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
                 tc_fence_after();
                 const uint32_t row_addr = lane_addr + ab * 256u; // X half
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    tmem_ld32(row_addr + (uint32_t)(c * 32), v);
-                    tmem_st32(row_addr + (uint32_t)(c * 32), z);
+                for (int c = 0; c < 4; ++c) { // own columns first; the other request's columns of this lane are only cleared
+                    const uint32_t col = (uint32_t)((cbase + c * 32) & 127);
+                    if (c < NCH) tmem_ld32(row_addr + col, v);
+                    tmem_st32(row_addr + col, z);
+                    if (c < NCH) {
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) row[c * 32 + e] += v[e];
+                        for (int e = 0; e < 32; ++e) row[c * 32 + e] += v[e];
+                    }
                 }
                 if (ch + 1 < nchunk) {
                     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
@@ -333,9 +360,9 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
             }
             float d = 0.f;
 #pragma unroll
-            for (int c = 0; c < 4; ++c)
+            for (int c = 0; c < NCH; ++c)
 #pragma unroll
-                for (int e = 0; e < 32; ++e) d = (c == ew && lane == e) ? row[c * 32 + e] : d;
+                for (int e = 0; e < 32; ++e) d = (c == ew - w0 && lane == e) ? row[c * 32 + e] : d;
             d = fmaf(2.f * kT16LoScale, yd, d); // S_ii = X_ii + 2^-11 * 2 Y_ii
             // range check (see the header): this candidate's norm must sit where fp16 pieces are exact enough
             const bool bad = act && !(d >= kT16MinNorm2 && d < __int_as_float(0x7f800000));
@@ -345,20 +372,23 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
             const float uis = ui * kT16LoScale;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
+                const uint32_t col = (uint32_t)((cbase + c * 32) & 127);
                 float cs = 0.f;
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
-                    const uint32_t ya = lane_addr + ((uint32_t)hh ^ first_ab) * 256u + 128u + (uint32_t)(c * 32);
-                    tmem_ld32(ya, v);
+                    const uint32_t ya = lane_addr + ((uint32_t)hh ^ first_ab) * 256u + 128u + col;
+                    if (c < NCH) tmem_ld32(ya, v);
                     tmem_st32(ya, z);
+                    if (c < NCH) {
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) {
-                        row[c * 32 + e] = fmaf(v[e], kT16LoScale, row[c * 32 + e]);
-                        v[e] *= uis;
+                        for (int e = 0; e < 32; ++e) {
+                            row[c * 32 + e] = fmaf(v[e], kT16LoScale, row[c * 32 + e]);
+                            v[e] *= uis;
+                        }
+                        cs += warp_transpose_sum<32>(v, lane);
                     }
-                    cs += warp_transpose_sum<32>(v, lane);
                 }
-                col_s[ew * 128 + c * 32 + lane] = cs;
+                if (c < NCH) col_s[ew * 128 + c * 32 + lane] = cs; // columns counted from the request's first
             }
             const bool warp_bad = __any_sync(kFullMask, bad);
             if (lane == 0) ipart[4 + ew] = warp_bad ? 1 : 0;
@@ -367,29 +397,32 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
             mbar_arrive(tempty0 + 8 * last_ab);
             mbar_arrive(yempty0);
             epi_sync();
-            const bool fix = (ipart[4] | ipart[5] | ipart[6] | ipart[7]) != 0;
-            if (i == 0 && fix_flags) fix_flags[r] = fix ? 1 : 0;
+            const bool fix = PAIR ? (ipart[4 + w0] | ipart[5 + w0]) != 0 : (ipart[4] | ipart[5] | ipart[6] | ipart[7]) != 0;
+            if (ii == 0 && exists && fix_flags) fix_flags[r] = fix ? 1 : 0;
             float acc = 0.f;
 #pragma unroll
-            for (int e = 0; e < 128; ++e) acc = fmaf(u_s[e], row[e], acc);
-            acc += (col_s[i] + col_s[128 + i]) + (col_s[256 + i] + col_s[384 + i]);
+            for (int e = 0; e < NCH * 32; ++e) acc = fmaf(u_s[cbase + e], row[e], acc);
+            if (PAIR)
+                acc += col_s[w0 * 128 + ii] + col_s[(w0 + 1) * 128 + ii];
+            else
+                acc += (col_s[i] + col_s[128 + i]) + (col_s[256 + i] + col_s[384 + i]);
             float c = act ? acc * rn : 0.f;
             // ---- tally (client.rs:422-449) with fixed-order block reductions
             float ws = warp_sum(c);
             if (lane == 0) part[ew] = ws;
             epi_sync();
-            const float sum = (part[0] + part[1]) + (part[2] + part[3]);
+            const float sum = PAIR ? part[w0] + part[w0 + 1] : (part[0] + part[1]) + (part[2] + part[3]);
             const bool positive = sum > 0.f;
             const float cf = (positive && act) ? c / sum : 0.f;
             cf_s[i] = cf;
-            const bool store = !fix; // a marked request is written by the fix-up pass
+            const bool store = !fix && exists; // a marked request is written by the fix-up pass
             if (act && store) {
-                if (p.cw) p.cw[(size_t)r * N + i] = c;
-                if (p.conf) p.conf[(size_t)r * N + i] = cf;
+                if (p.cw) p.cw[(size_t)r * N + ii] = c;
+                if (p.conf) p.conf[(size_t)r * N + ii] = cf;
             }
             if (p.winner) {
                 float bv = act ? cf : -1.f;
-                int bi = act ? i : 0x7fffffff;
+                int bi = act ? ii : 0x7fffffff;
                 warp_argmax(bv, bi);
                 if (lane == 0) {
                     part[4 + ew] = bv;
@@ -397,45 +430,46 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
                 }
             }
             epi_sync();
-            if (p.winner && i == 0 && store) {
-                float best = part[4];
-                int besti = ipart[0];
+            if (p.winner && ii == 0 && store) {
+                float best = part[4 + w0];
+                int besti = ipart[w0];
 #pragma unroll
-                for (int k = 1; k < 4; ++k)
-                    if (part[4 + k] > best || (part[4 + k] == best && ipart[k] < besti)) {
-                        best = part[4 + k];
-                        besti = ipart[k];
+                for (int k = 1; k < (PAIR ? 2 : 4); ++k)
+                    if (part[4 + w0 + k] > best || (part[4 + w0 + k] == best && ipart[w0 + k] < besti)) {
+                        best = part[4 + w0 + k];
+                        besti = ipart[w0 + k];
                     }
                 p.winner[r] = positive ? besti : -1;
             }
             if (p.rank && act && store) {
                 int pos = 0;
                 for (int j = 0; j < N; ++j) {
-                    const float cj = cf_s[j];
-                    pos += (cj > cf || (cj == cf && j < i)) ? 1 : 0;
+                    const float cj = cf_s[cbase + j];
+                    pos += (cj > cf || (cj == cf && j < ii)) ? 1 : 0;
                 }
-                p.rank[(size_t)r * N + pos] = i;
+                p.rank[(size_t)r * N + pos] = ii;
             }
             if (p.agree && store) {
-                for (int m0 = ew; m0 < M; m0 += 16) {
+                constexpr int NW = PAIR ? 2 : 4; // warps sharing this request's voters
+                for (int m0 = ew - w0; m0 < M; m0 += 4 * NW) {
                     float v0[4], s4[4];
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        const int m = m0 + 4 * u;
+                        const int m = m0 + NW * u;
                         v0[u] = m < M ? __ldg(Vr + (size_t)m * N) : 0.f;
                         s4[u] = 0.f;
                     }
                     for (int j = lane; j < N; j += 32) {
-                        const float cj = cf_s[j];
+                        const float cj = cf_s[cbase + j];
 #pragma unroll
                         for (int u = 0; u < 4; ++u) {
-                            const int m = m0 + 4 * u;
+                            const int m = m0 + NW * u;
                             if (m < M) s4[u] = fmaf(cj, __ldg(Vr + (size_t)m * N + j), s4[u]);
                         }
                     }
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        const int m = m0 + 4 * u;
+                        const int m = m0 + NW * u;
                         if (m >= M) break;
                         const float a = isnan(v0[u]) ? __int_as_float(0x7fc00000) : warp_sum(s4[u]);
                         if (lane == 0) p.agree[(size_t)r * M + m] = a;

@@ -64,7 +64,7 @@ TC_REGIME = [(600, 128, 3072, 16), (600, 128, 2304, 16), (600, 40, 3072, 16), (6
 @pytest.mark.parametrize("shape", TC_REGIME, ids=lambda s: "R%d_N%d_D%d_M%d" % s)
 def test_tcgen05_fp32_grade_many_requests_per_cta(ctx, lwc, oracle, shape):
     R, N, D, M = shape
-    assert ctx.kernel_for(R, N, D, M) == "tc128_f16x2"
+    assert ctx.kernel_for(R, N, D, M) == ("tc64x2_f16x2" if N <= 64 else "tc128_f16x2")
     E, V, w = fast_batch(R, N, D, M, seed=90 + N + D)
     got = ctx.score_batch_device(E, V, w)
     want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
@@ -80,7 +80,7 @@ def test_tcgen05_fp32_grade_many_requests_per_cta(ctx, lwc, oracle, shape):
 @pytest.mark.parametrize("shape", TC_REGIME, ids=lambda s: "R%d_N%d_D%d_M%d" % s)
 def test_tcgen05_tf32_many_requests_per_cta(ctx, lwc, oracle, shape):
     R, N, D, M = shape
-    assert ctx.kernel_for(R, N, D, M, precision=lwc.PREC_TF32) == "tc128_tf32"
+    assert ctx.kernel_for(R, N, D, M, precision=lwc.PREC_TF32) == ("tc64x2_tf32" if N <= 64 else "tc128_tf32")
     E, V, w = fast_batch(R, N, D, M, seed=190 + N + D)
     got = ctx.score_batch_device(E, V, w, precision=lwc.PREC_TF32)
     want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
@@ -305,6 +305,81 @@ def test_fp16_piece_route_fixes_up_requests_outside_fp16_range(ctx, lwc, oracle)
     again = ctx.score_batch_device(E[perm], V[perm], w[perm])
     for k in got:
         assert np.array_equal(again[k], got[k][perm], equal_nan=True), k
+
+
+PAIR_SHAPES = [(601, 64, 1024, 8), (333, 33, 2304, 3), (1, 48, 256, 4), (2, 64, 96, 16), (299, 57, 2336, 5), (1201, 40, 512, 0)]
+
+
+@pytest.mark.parametrize("shape", PAIR_SHAPES, ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+def test_two_requests_per_tile_route(lwc, oracle, shape):
+    """Pools of 33..64 candidates at the default precision ride two to a 128-row tcgen05 tile (score_tc16_kernel<PAIR>):
+    each request must meet the fp32 bar, must not see its tile partner (the same request next to a different partner, or
+    alone at the end of an odd batch, gives the same bits), and the range check / fix-up pass works per request."""
+    R, N, D, M = shape
+    E, V, w = fast_batch(R, N, D, max(M, 1), seed=300 + N + D)
+    if M == 0:
+        V, w = V[:, :0], w[:, :0]
+    if R > 8:
+        E[3] *= np.float32(1e-6)     # marked: fix-up pass rewrites it; its partner (request 2) stays on the fast pass
+        E[6, N - 1, :] = 0.0         # a zero-norm candidate marks request 6
+        E[R - 1, 0, 1] = 7e4         # the odd batch's last request, alone in its tile, out of fp16 range
+    with lwc.Context(device=0) as c:
+        assert c.kernel_for(R, N, D, M) == "tc64x2_f16x2"
+        got = c.score_batch_device(E, V, w)
+        again = c.score_batch_device(E, V, w)
+        want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+        assert compare(got, want, V) == 1.0
+        properties_hold(got, V)
+        assert all(np.array_equal(got[k], again[k], equal_nan=True) for k in got)
+        if R > 8:
+            perm = np.random.default_rng(8).permutation(R)[: R - 1 if R % 2 else R - 3]  # other partners, other halves
+            moved = c.score_batch_device(E[perm], V[perm], w[perm])
+            for k in got:
+                assert np.array_equal(moved[k], got[k][perm], equal_nan=True), k
+    old = os.environ.get("LWC_TC_PAIR")
+    try:
+        os.environ["LWC_TC_PAIR"] = "0"  # one request per tile: same arithmetic on the same accumulator entries
+        with lwc.Context(device=0) as c:
+            assert c.kernel_for(R, N, D, M) == "tc128_f16x2"
+            single = c.score_batch_device(E, V, w)
+    finally:
+        if old is None:
+            os.environ.pop("LWC_TC_PAIR", None)
+        else:
+            os.environ["LWC_TC_PAIR"] = old
+    assert compare(single, want, V) == 1.0
+    assert np.array_equal(single["winner"], got["winner"])
+    np.testing.assert_allclose(single["conf"], got["conf"], rtol=2e-6, atol=1e-9)
+
+
+@pytest.mark.parametrize("shape", PAIR_SHAPES, ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+def test_two_requests_per_tile_route_tf32(lwc, oracle, shape):
+    """The same pairing on the single-pass TF32 route (score_tc_kernel<false, PAIR>): stated TF32 tolerance against the
+    oracle, and bit-equal to the one-request-per-tile kernel -- every accumulator entry a request reads is produced by
+    the same MMAs on the same operands, and its reductions add the same terms in the same order."""
+    R, N, D, M = shape
+    E, V, w = fast_batch(R, N, D, max(M, 1), seed=400 + N + D)
+    if M == 0:
+        V, w = V[:, :0], w[:, :0]
+    with lwc.Context(device=0) as c:
+        assert c.kernel_for(R, N, D, M, precision=lwc.PREC_TF32) == "tc64x2_tf32"
+        got = c.score_batch_device(E, V, w, precision=lwc.PREC_TF32)
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    compare(got, want, V, rtol=2e-3, atol=1e-5, gap=5e-3, min_agreement=0.95, atol_of_max=2e-3)
+    properties_hold(got, V)
+    old = os.environ.get("LWC_TC_PAIR")
+    try:
+        os.environ["LWC_TC_PAIR"] = "0"
+        with lwc.Context(device=0) as c:
+            assert c.kernel_for(R, N, D, M, precision=lwc.PREC_TF32) == "tc128_tf32"
+            single = c.score_batch_device(E, V, w, precision=lwc.PREC_TF32)
+    finally:
+        if old is None:
+            os.environ.pop("LWC_TC_PAIR", None)
+        else:
+            os.environ["LWC_TC_PAIR"] = old
+    for k in got:
+        assert np.array_equal(single[k], got[k], equal_nan=True), k
 
 
 @pytest.mark.parametrize("shape", [(600, 128, 3072, 16), (600, 100, 2304, 16), (300, 40, 96, 3)], ids=lambda s: "R%d_N%d_D%d_M%d" % s)
