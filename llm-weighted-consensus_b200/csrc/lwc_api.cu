@@ -306,7 +306,7 @@ cudaError_t ensure_fix_flags(lwc_ctx *ctx, int R) {
 }
 
 // list != nullptr: one launch over a list of same-shaped batches (score_stream_list_kernel); p.R = all requests of the list
-template <int NT, bool X3, int NCW, int NF>
+template <int NT, bool X3, int NCW, int NF, int NB = NT / 8>
 cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st, const lwc::ScoreList *list = nullptr) {
     using C = lwc::StreamCfg<NT, X3, NCW, NF>;
     const size_t avail = (size_t)ctx->max_smem_optin - 128 - C::fixed_bytes();
@@ -324,10 +324,10 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
     if (geo.stages < 1) return cudaErrorInvalidConfiguration;
     static std::atomic<bool> configured[64]; // zero-initialised; set once per device (contexts on other threads may race here)
     if (!configured[ctx->device & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(lwc::score_stream_kernel<NT, X3, NCW, NF>,
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_stream_kernel<NT, X3, NCW, NF, NB>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(lwc::score_stream_list_kernel<NT, X3, NCW, NF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            e = cudaFuncSetAttribute(lwc::score_stream_list_kernel<NT, X3, NCW, NF, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      ctx->max_smem_optin);
         if (e != cudaSuccess) return e;
         configured[ctx->device & 63] = true;
@@ -343,14 +343,16 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (list) return cudaLaunchKernelEx(&cfg, lwc::score_stream_list_kernel<NT, X3, NCW, NF>, p, geo, *list);
-    return cudaLaunchKernelEx(&cfg, lwc::score_stream_kernel<NT, X3, NCW, NF>, p, geo);
+    if (list) return cudaLaunchKernelEx(&cfg, lwc::score_stream_list_kernel<NT, X3, NCW, NF, NB>, p, geo, *list);
+    return cudaLaunchKernelEx(&cfg, lwc::score_stream_kernel<NT, X3, NCW, NF, NB>, p, geo);
 }
 
 template <int NT, bool X3>
 cudaError_t launch_stream(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st) {
     const int ncw = ctx->stream_ncw ? ctx->stream_ncw : (NT == 16 ? 12 : 8);
     const int nf = ctx->stream_nf ? ctx->stream_nf : (NT == 16 ? 4 : 2);
+    // pools of at most 8 candidates: the half-tile form (score_stream.cuh, NB = 1); LWC_STREAM_HALF=0 keeps the full tile
+    if (NT == 16 && p.N <= 8 && !ctx->stream_no_half && ncw == 12 && nf == 4) return launch_stream_one<16, X3, 12, 4, 1>(ctx, p, st);
     switch (ncw * 10 + nf) {
         case 41: return launch_stream_one<NT, X3, 4, 1>(ctx, p, st);
         case 42: return launch_stream_one<NT, X3, 4, 2>(ctx, p, st);
@@ -396,7 +398,9 @@ bool list_route(const lwc_ctx *ctx, const Plan &pl) {
 }
 int launch_list(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, const lwc::ScoreList &list, cudaStream_t st) {
     cudaError_t e;
-    if (pl.np == 16)
+    if (pl.np == 16 && p.N <= 8 && !ctx->stream_no_half)
+        e = pl.x3 ? launch_stream_one<16, true, 12, 4, 1>(ctx, p, st, &list) : launch_stream_one<16, false, 12, 4, 1>(ctx, p, st, &list);
+    else if (pl.np == 16)
         e = pl.x3 ? launch_stream_one<16, true, 12, 4>(ctx, p, st, &list) : launch_stream_one<16, false, 12, 4>(ctx, p, st, &list);
     else
         e = pl.x3 ? launch_stream_one<32, true, 8, 2>(ctx, p, st, &list) : launch_stream_one<32, false, 8, 2>(ctx, p, st, &list);
@@ -705,6 +709,7 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     if (const char *s = getenv("LWC_TC_KO")) ctx->tc_ko = atoi(s);
     if (const char *s = getenv("LWC_TC_X3")) ctx->tc_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_TC_PAIR")) ctx->tc_no_pair = atoi(s) == 0 ? 1 : 0;
+    if (const char *s = getenv("LWC_STREAM_HALF")) ctx->stream_no_half = atoi(s) == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_X3")) ctx->small_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_PIPE")) ctx->small_pipe = atoi(s);
     if (const char *s = getenv("LWC_SMALL_ZERO_COPY")) ctx->small_zero_copy = atoi(s);

@@ -139,10 +139,16 @@ __device__ __forceinline__ ScoreParams list_params(const ScoreParams &p, const S
     return q;
 }
 
-template <int NT, bool X3, int NCW, int NFIN, bool LIST>
+// NB: 8-column MMA tiles (= 8-row groups) that can hold candidates.  NB = NT / 8 is the full tile; NB = 1 with NT = 16 is
+// the form for pools of at most 8 candidates: rows 8..15 are neither loaded nor multiplied (their A registers are
+// constant zeros), the second column tile is never computed -- half the shared-memory loads, piece splits and MMAs of
+// a request, which is what bounds this kernel when a request brings half the bytes.
+template <int NT, bool X3, int NCW, int NFIN, bool LIST, int NB = NT / 8>
 __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const StreamGeom &geo, const ScoreList *list) {
     using C = StreamCfg<NT, X3, NCW, NFIN>;
-    constexpr int RPL = C::RPL, MT = C::MT, NTL = C::NTL, NF = C::NF;
+    constexpr int RPL = C::RPL, MT = C::MT, NF = C::NF;
+    constexpr int NTL = NB; // column tiles in use (C::NTL of them have room in the park buffer and the S tile)
+    static_assert(NB >= 1 && NB <= C::NTL && (NB == C::NTL || MT == 1), "NB < NT/8 only for one 16-row tile");
     constexpr int TPITCH = C::TPITCH, NACC = C::NACC, MAXS = C::MAXS;
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -255,7 +261,7 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
                     float4 v[RPL];
 #pragma unroll
                     for (int qq = 0; qq < RPL; ++qq)
-                        v[qq] = *reinterpret_cast<const float4 *>(base + qq * 8 * pitchb + c * 64);
+                        v[qq] = qq < NB ? *reinterpret_cast<const float4 *>(base + qq * 8 * pitchb + c * 64) : make_float4(0.f, 0.f, 0.f, 0.f);
                     if (c * 16 + 16 > kv && c * 16 + 4 * t4 >= kv) { // ragged tail: stale bytes beyond D
 #pragma unroll
                         for (int qq = 0; qq < RPL; ++qq) v[qq] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -265,6 +271,10 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
                         uint32_t xh[RPL], yh[RPL], xl[RPL], yl[RPL];
 #pragma unroll
                         for (int qq = 0; qq < RPL; ++qq) {
+                            if (qq >= NB) { // no candidates in these rows: constant zero operands
+                                xh[qq] = yh[qq] = xl[qq] = yl[qq] = 0u;
+                                continue;
+                            }
                             const float x = h ? v[qq].z : v[qq].x;
                             const float y = h ? v[qq].w : v[qq].y;
                             if (X3) {
@@ -436,26 +446,26 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
         if (LIST) {
             int rl;
             const ScoreParams pb = list_params(p, list, r, &rl);
-            warp_tally_and_rank_pf<kVotePrefetch, NT>(pb, rl, tile, TPITCH, lane, pv, pw);
+            warp_tally_and_rank_pf<kVotePrefetch, NB * 8>(pb, rl, tile, TPITCH, lane, pv, pw);
         } else {
-            warp_tally_and_rank_pf<kVotePrefetch, NT>(p, r, tile, TPITCH, lane, pv, pw);
+            warp_tally_and_rank_pf<kVotePrefetch, NB * 8>(p, r, tile, TPITCH, lane, pv, pw);
         }
         __syncwarp();
         if (q + NF < nreq) prefetch_votes(r + NF);
     }
 }
 
-template <int NT, bool X3, int NCW, int NFIN>
+template <int NT, bool X3, int NCW, int NFIN, int NB = NT / 8>
 __global__ void __launch_bounds__((1 + NCW + NFIN) * 32, 1)
 score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
-    score_stream_body<NT, X3, NCW, NFIN, false>(p, geo, nullptr);
+    score_stream_body<NT, X3, NCW, NFIN, false, NB>(p, geo, nullptr);
 }
 
 // p.R = list.n * list.R_each; p's own pointers are unused
-template <int NT, bool X3, int NCW, int NFIN>
+template <int NT, bool X3, int NCW, int NFIN, int NB = NT / 8>
 __global__ void __launch_bounds__((1 + NCW + NFIN) * 32, 1)
 score_stream_list_kernel(const ScoreParams p, const StreamGeom geo, const __grid_constant__ ScoreList list) {
-    score_stream_body<NT, X3, NCW, NFIN, true>(p, geo, &list);
+    score_stream_body<NT, X3, NCW, NFIN, true, NB>(p, geo, &list);
 }
 
 } // namespace lwc
