@@ -29,15 +29,19 @@
 //   warp 1 (1 lane)    MMA issuer: per unit 4 x tcgen05.mma.kind::f16 (M = 128, N = 256, K = 16), A = the h tile,
 //                      B = the 256-row pair [h ; l]: accumulator [X | Y], 2 x 256 TMEM columns double-buffered.
 //   warps 4..7         epilogue, as score_tc_kernel<true>: X restarts every chunk of kT16ChunkUnits units (the
-//                      tensor core's fp32 accumulator truncates; chunks are summed in registers), Y runs through
-//                      the request, S_ij = X_ij + 2^-11 (Y_ij + Y_ji) via the row / warp-transpose fold.
+//                      tensor core's fp32 accumulator truncates; chunks are summed in registers; the restart is the
+//                      chunk's first MMA issued with the accumulate flag off), Y runs through the request,
+//                      S_ij = X_ij + 2^-11 (Y_ij + Y_ji) via the row / warp-transpose fold.
 // Shared-memory traffic per unit: 32 KB TMA in, 32 + 32 KB transform, 16 + 32 KB operand reads = 144 KB against
 // the 192 KB per 64 columns of the tf32 scheme; tensor time 4 x 187 clk against ~1,480 clk a unit has at HBM speed.
 // Measured (cfg4, 8,192 requests): 2.61 ms against 3.03 ms on tf32 pieces and 1.91 ms for the single-pass TF32 route on
 // the same box -- 0.77 of HBM.  Bound: the SHARED-MEMORY pipe (ncu, profiles/r2_tc16_raw.csv: LSU wavefronts 50 % +
 // tensor operand reads 24 % + TMA writes; tensor pipe 33 %, DRAM 5.0 TB/s): 144 KB of shared-memory traffic per 32 KB of
 // HBM traffic.  Tried and dropped: asking L2 for the units eight ahead of the ring (cp.async.bulk.prefetch.tensor) so
-// that HBM latency stops depending on ring depth -- 2.80 ms, i.e. latency was not the limit.
+// that HBM latency stops depending on ring depth -- 2.80 ms, i.e. latency was not the limit.  Kept, for ~1 % each on
+// cfg4 (2.606 -> 2.585 -> 2.579 ms on one box, scripts/r2_ab_tc16.sh): one "Y read" barrier per accumulator, the one the
+// next request starts on released first; and no TMEM clearing stores at all (the first MMA of a chunk runs with the
+// accumulate flag off) -- the request-boundary bubble was never the limit either.
 #pragma once
 
 #include <cuda_fp16.h>
@@ -69,12 +73,13 @@ constexpr float kT16MinNorm2 = 1.0f / 4096.0f;  // squared norm below which fp16
 __device__ __forceinline__ constexpr uint32_t umma_idesc_f16(int M, int N) {
     return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
-__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc) {
+// acc = 0: D = A B^T (the accumulator's old contents are ignored); acc = 1: D += A B^T
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, 1, 0;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc)
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
         : "memory");
 }
 
@@ -136,7 +141,7 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
         for (int b = 0; b < 2; ++b) {
             mbar_init(tfull0 + 8 * b, 1);
             mbar_init(tempty0 + 8 * b, 128);
-            mbar_init(yempty0 + 8 * b, 128); // only [0] is used
+            mbar_init(yempty0 + 8 * b, 128); // one per accumulator: its Y half drained and zeroed (previous request)
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -150,18 +155,8 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    // the MMAs always accumulate ([X | Y] in one tile, X restarted per chunk, Y not): the epilogue threads zero what
-    // must restart; at the start, everything
-    if (warp >= 4 && warp < 8) {
-        uint32_t z[32];
-#pragma unroll
-        for (int e = 0; e < 32; ++e) z[e] = 0u;
-        for (int c = 0; c < 16; ++c) tmem_st32(tmem_base + ((uint32_t)((warp - 4) * 32) << 16) + (uint32_t)(c * 32), z);
-        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-    }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
+    // Nothing in TMEM is ever cleared by a store: the first MMA of a chunk starts X afresh (accumulate flag off), and Y
+    // starts afresh with each accumulator's first chunk of a request (see the MMA issuer).
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -188,7 +183,7 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
         // ===================== MMA issuer =====================
         if (lane == 0) {
             const uint32_t ring_u32 = smem_u32(ring);
-            const uint32_t idesc = umma_idesc_f16(128, 256);
+            const uint32_t idesc = umma_idesc_f16(128, 256), idesc_half = umma_idesc_f16(128, 128);
             int slot = 0;
             uint32_t phase = 0;
             uint32_t tile = 0; // accumulator hand-offs so far: one per chunk
@@ -197,14 +192,18 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
                 mbar_wait(tempty0 + 8 * ab, ((tile >> 1) & 1u) ^ 1u);
                 tc_fence_after();
                 uint32_t d_tmem = tmem_base + ab * 256u;
-                mbar_wait(yempty0, ((uint32_t)q & 1u) ^ 1u); // both Y halves drained and zeroed (previous request)
+                // the Y half of THIS accumulator drained and zeroed by the epilogue of the previous request (it drains
+                // the half the next request starts on first, so that this wait is as short as it can be)
+                mbar_wait(yempty0 + 8 * ab, ((uint32_t)q & 1u) ^ 1u);
                 tc_fence_after();
                 for (int u = 0; u < upr; ++u) {
-                    if (u > 0 && u % kT16ChunkUnits == 0) { // chunk boundary: hand over, switch accumulator
+                    const bool chunk_start = u % kT16ChunkUnits == 0;
+                    if (u > 0 && chunk_start) { // chunk boundary: hand over, switch accumulator
                         umma_commit(tfull0 + 8 * ab);
                         ++tile;
                         ab = tile & 1u;
                         mbar_wait(tempty0 + 8 * ab, ((tile >> 1) & 1u) ^ 1u);
+                        if (u == kT16ChunkUnits) mbar_wait(yempty0 + 8 * ab, ((uint32_t)q & 1u) ^ 1u); // first use of the other accumulator
                         tc_fence_after();
                         d_tmem = tmem_base + ab * 256u;
                     }
@@ -214,7 +213,18 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
 #pragma unroll
                     for (int kk = 0; kk < 4; ++kk) { // 4 x K = 16 inside the 128-byte swizzle atom
                         const uint64_t d = umma_desc_sw128(unit + kk * 32);
-                        umma_f16(d_tmem, d, d, idesc); // A: 128 rows = h; B: 256 rows = [h ; l]
+                        if (kk == 0 && chunk_start) {
+                            // X restarts with every chunk; Y with this accumulator's first chunk of the request (chunks 0
+                            // and 1).  Later chunks: X afresh, Y on top of what the accumulator holds -- two half-width MMAs.
+                            if (u < 2 * kT16ChunkUnits) {
+                                umma_f16(d_tmem, d, d, idesc, 0u);
+                            } else {
+                                umma_f16(d_tmem, d, d, idesc_half, 0u);                                                     // X = h h^T
+                                umma_f16(d_tmem + 128u, d, umma_desc_sw128(unit + kTcSlabBytes + kk * 32), idesc_half, 1u); // Y += h l^T
+                            }
+                        } else {
+                            umma_f16(d_tmem, d, d, idesc, 1u); // A: 128 rows = h; B: 256 rows = [h ; l]
+                        }
                     }
                     umma_commit(empty0 + 8 * slot);
                     if (++slot == S) {
@@ -324,9 +334,6 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
             float row[NCH * 32]; // this candidate's row of S over its own request's columns
 #pragma unroll
             for (int e = 0; e < NCH * 32; ++e) row[e] = 0.f;
-            uint32_t z[32];
-#pragma unroll
-            for (int e = 0; e < 32; ++e) z[e] = 0u;
             const uint32_t first_ab = tile & 1u; // accumulator of this request's even chunks (see score_tc.cuh)
             for (int ch = 0; ch < nchunk; ++ch, ++tile) {
                 const uint32_t ab = tile & 1u;
@@ -334,17 +341,12 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
                 tc_fence_after();
                 const uint32_t row_addr = lane_addr + ab * 256u; // X half
 #pragma unroll
-                for (int c = 0; c < 4; ++c) { // own columns first; the other request's columns of this lane are only cleared
-                    const uint32_t col = (uint32_t)((cbase + c * 32) & 127);
-                    if (c < NCH) tmem_ld32(row_addr + col, v);
-                    tmem_st32(row_addr + col, z);
-                    if (c < NCH) {
+                for (int c = 0; c < NCH; ++c) { // the request's own columns
+                    tmem_ld32(row_addr + (uint32_t)(cbase + c * 32), v);
 #pragma unroll
-                        for (int e = 0; e < 32; ++e) row[c * 32 + e] += v[e];
-                    }
+                    for (int e = 0; e < 32; ++e) row[c * 32 + e] += v[e];
                 }
-                if (ch + 1 < nchunk) {
-                    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                if (ch + 1 < nchunk) { // X read: the accumulator's next chunk may overwrite it
                     tc_fence_before();
                     mbar_arrive(tempty0 + 8 * ab);
                 }
@@ -353,6 +355,7 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
             float yd = 0.f;
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
+                if (hh == 1 && nchunk == 1) break; // a one-chunk request used one accumulator: the other holds nothing of it
                 const uint32_t h = (uint32_t)hh ^ first_ab;
                 tmem_ld32(lane_addr + h * 256u + 128u + (uint32_t)(ew * 32), v);
 #pragma unroll
@@ -370,32 +373,36 @@ score_tc16_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p, 
             const float ui = t * rn;
             u_s[i] = ui;
             const float uis = ui * kT16LoScale;
+            // The accumulator the NEXT request starts on (the one that is not last_ab) is read first and handed back at
+            // once; the other one's fold then overlaps that request's first chunk.  With an even chunk count that is the
+            // first_ab-then-other order of score_tc.cuh; with an odd count the halves swap -- either way the order is a
+            // function of the request's own chunk parities, not of its position in the batch.
+            float cs[NCH];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const uint32_t col = (uint32_t)((cbase + c * 32) & 127);
-                float cs = 0.f;
+            for (int c = 0; c < NCH; ++c) cs[c] = 0.f;
 #pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {
-                    const uint32_t ya = lane_addr + ((uint32_t)hh ^ first_ab) * 256u + 128u + col;
-                    if (c < NCH) tmem_ld32(ya, v);
-                    tmem_st32(ya, z);
-                    if (c < NCH) {
+            for (int hh = 0; hh < 2; ++hh) {
+                const uint32_t h = (uint32_t)hh ^ last_ab ^ 1u;
+                if (hh == 1 || nchunk > 1) { // a one-chunk request never touched the other accumulator
+#pragma unroll
+                    for (int c = 0; c < NCH; ++c) {
+                        tmem_ld32(lane_addr + h * 256u + 128u + (uint32_t)(cbase + c * 32), v);
 #pragma unroll
                         for (int e = 0; e < 32; ++e) {
                             row[c * 32 + e] = fmaf(v[e], kT16LoScale, row[c * 32 + e]);
                             v[e] *= uis;
                         }
-                        cs += warp_transpose_sum<32>(v, lane);
+                        cs[c] += warp_transpose_sum<32>(v, lane);
                     }
                 }
-                if (c < NCH) col_s[ew * 128 + c * 32 + lane] = cs; // columns counted from the request's first
+                tc_fence_before();
+                if (hh == 1) mbar_arrive(tempty0 + 8 * last_ab); // the last chunk's X was read in the chunk loop
+                mbar_arrive(yempty0 + 8 * h);
             }
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) col_s[ew * 128 + c * 32 + lane] = cs[c]; // columns counted from the request's first
             const bool warp_bad = __any_sync(kFullMask, bad);
             if (lane == 0) ipart[4 + ew] = warp_bad ? 1 : 0;
-            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-            tc_fence_before();
-            mbar_arrive(tempty0 + 8 * last_ab);
-            mbar_arrive(yempty0);
             epi_sync();
             const bool fix = PAIR ? (ipart[4 + w0] | ipart[5 + w0]) != 0 : (ipart[4] | ipart[5] | ipart[6] | ipart[7]) != 0;
             if (ii == 0 && exists && fix_flags) fix_flags[r] = fix ? 1 : 0;
