@@ -314,11 +314,14 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
     // stage width: 3 KB per row copy is where the bulk-copy engine reaches HBM speed
     // (profiles/r1_tma_probe.txt); shrink it until at least 3 stages fit.
     const int dpad = (p.D + 15) / 16 * 16;
-    int ks = ctx->stream_kc >= 16 ? ctx->stream_kc : 768;
+    constexpr int rows = NB * 8; // rows per stage
+    // (half-tile form: 6 KB per row copy -- its stages hold half the rows, and a stage hand-off costs the consumers the
+    // same whatever it carries: 0.84 -> 0.98 of HBM at 8 candidates x 3072, profiles/r2_pool_sizes.jsonl)
+    int ks = ctx->stream_kc >= 16 ? ctx->stream_kc : (NB * 8 < NT ? 1536 : 768);
     if (ks > dpad) ks = dpad;
-    while (ks > 64 && avail / C::stage_bytes(ks) < 3) ks = ((ks / 2) + 15) / 16 * 16;
+    while (ks > 64 && avail / C::stage_bytes(ks, rows) < 3) ks = ((ks / 2) + 15) / 16 * 16;
     geo.ks = ks;
-    geo.stages = (int)(avail / C::stage_bytes(ks));
+    geo.stages = (int)(avail / C::stage_bytes(ks, rows));
     if (geo.stages > C::MAXS) geo.stages = C::MAXS;
     if (ctx->stream_slots >= 1 && ctx->stream_slots < geo.stages) geo.stages = ctx->stream_slots;
     if (geo.stages < 1) return cudaErrorInvalidConfiguration;
@@ -336,7 +339,7 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(C::THREADS);
-    cfg.dynamicSmemBytes = C::smem_bytes(geo.ks, geo.stages);
+    cfg.dynamicSmemBytes = C::smem_bytes(geo.ks, geo.stages, rows);
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; // pairs with griddepcontrol.* in the kernel

@@ -110,8 +110,9 @@ struct StreamCfg {
     static constexpr size_t TILE_BYTES = (size_t)NF * NT * TPITCH * sizeof(float);
     static constexpr size_t BAR_BYTES = (size_t)(2 * MAXS + 2 + NF) * sizeof(uint64_t);
     static constexpr size_t fixed_bytes() { return RED_BYTES + TILE_BYTES + BAR_BYTES + 128; }
-    static constexpr size_t stage_bytes(int ks) { return (size_t)NT * (ks * sizeof(float) + 64); }
-    static constexpr size_t smem_bytes(int ks, int stages) { return fixed_bytes() + (size_t)stages * stage_bytes(ks); }
+    // rows: candidate rows a stage has room for (NT, or 8 in the half-tile form: twice the stages, twice the bytes in flight)
+    static constexpr size_t stage_bytes(int ks, int rows = NT) { return (size_t)rows * (ks * sizeof(float) + 64); }
+    static constexpr size_t smem_bytes(int ks, int stages, int rows = NT) { return fixed_bytes() + (size_t)stages * stage_bytes(ks, rows); }
 };
 
 constexpr bool kStreamFlush = kMmaChain < (1 << 20); // A/B builds (-DLWC_MMA_CHAIN=1000000) compile the flush out
@@ -154,8 +155,9 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int KS = geo.ks, S = geo.stages;
     const int pitchb = KS * 4 + 64;  // bytes between candidate rows of a stage: 64 (mod 128)
-    const int stageb = NT * pitchb;  // bytes per stage
-    unsigned char *ring = smem_raw;                                    // [S][NT][pitchb]
+    constexpr int SROWS = NB * 8;        // candidate rows a stage holds
+    const int stageb = SROWS * pitchb;   // bytes per stage
+    unsigned char *ring = smem_raw;                                    // [S][SROWS][pitchb]
     float *red = reinterpret_cast<float *>(ring + (size_t)S * stageb); // [NCW][NACC][32]
     float *tiles = red + (size_t)NCW * NACC * 32;                      // [NF][NT][TPITCH]
     uint64_t *bars = reinterpret_cast<uint64_t *>(tiles + (size_t)NF * NT * TPITCH);
@@ -170,7 +172,7 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
     const int spr = (D + KS - 1) / KS; // stages per request
 
     // rows >= N are never written by a copy and must read as zeros
-    if (N < NT) {
+    if (N < SROWS) {
         float4 *z = reinterpret_cast<float4 *>(ring);
         const int n16 = S * stageb / 16;
         for (int i = threadIdx.x; i < n16; i += C::THREADS) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
