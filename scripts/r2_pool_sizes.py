@@ -12,7 +12,7 @@ from lwc_b200 import synth
 def main():
     torch.cuda.set_device(0)
     peak, _ = bench.load_peaks()
-    D, M = 3072, 8
+    D, M = 3072, int(sys.argv[2]) if len(sys.argv) > 2 else 8
     sizes = [int(x) for x in (sys.argv[1].split(",") if len(sys.argv) > 1 else "8,16,24,32,40,48,64,80,96,128".split(","))]
     for N in sizes:
         R = max(256, int(1.6e9 / (N * D * 4)))
