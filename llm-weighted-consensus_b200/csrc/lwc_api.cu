@@ -153,19 +153,19 @@ cudaError_t launch_small_one(const lwc::ScoreParams &p, cudaStream_t st) {
 }
 
 // the cfg3 route: 32-row fp32-grade pools, fp16 pieces, loads pipelined through PS shared-memory stages
-template <int PS>
+template <int PS, int NB = 4>
 cudaError_t launch_small_pipe32(const lwc::ScoreParams &p, cudaStream_t st) {
     constexpr size_t smem = lwc::small_smem_bytes<32, true, 2, 2, PS>();
     static std::atomic<bool> configured[64];
     int dev = 0;
     cudaGetDevice(&dev);
     if (!configured[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(lwc::score_small_kernel<32, true, 2, 2, true, PS>,
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_small_kernel<32, true, 2, 2, true, PS, NB>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured[dev & 63] = true;
     }
-    lwc::score_small_kernel<32, true, 2, 2, true, PS><<<p.R, 64, smem, st>>>(p);
+    lwc::score_small_kernel<32, true, 2, 2, true, PS, NB><<<p.R, 64, smem, st>>>(p);
     return cudaGetLastError();
 }
 
@@ -317,7 +317,7 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
     constexpr int rows = NB * 8; // rows per stage
     // (half-tile form: 6 KB per row copy -- its stages hold half the rows, and a stage hand-off costs the consumers the
     // same whatever it carries: 0.84 -> 0.98 of HBM at 8 candidates x 3072, profiles/r2_pool_sizes.jsonl)
-    int ks = ctx->stream_kc >= 16 ? ctx->stream_kc : (NB * 8 < NT ? 1536 : 768);
+    int ks = ctx->stream_kc >= 16 ? ctx->stream_kc : (NB == 1 ? 1536 : 768);
     if (ks > dpad) ks = dpad;
     while (ks > 64 && avail / C::stage_bytes(ks, rows) < 3) ks = ((ks / 2) + 15) / 16 * 16;
     geo.ks = ks;
@@ -356,6 +356,7 @@ cudaError_t launch_stream(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t 
     const int nf = ctx->stream_nf ? ctx->stream_nf : (NT == 16 ? 4 : 2);
     // pools of at most 8 candidates: the half-tile form (score_stream.cuh, NB = 1); LWC_STREAM_HALF=0 keeps the full tile
     if (NT == 16 && p.N <= 8 && !ctx->stream_no_half && ncw == 12 && nf == 4) return launch_stream_one<16, X3, 12, 4, 1>(ctx, p, st);
+    if (NT == 32 && p.N <= 24 && !ctx->stream_no_half && ncw == 8 && nf == 2) return launch_stream_one<32, X3, 8, 2, 3>(ctx, p, st);
     switch (ncw * 10 + nf) {
         case 41: return launch_stream_one<NT, X3, 4, 1>(ctx, p, st);
         case 42: return launch_stream_one<NT, X3, 4, 2>(ctx, p, st);
@@ -405,6 +406,8 @@ int launch_list(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, const l
         e = pl.x3 ? launch_stream_one<16, true, 12, 4, 1>(ctx, p, st, &list) : launch_stream_one<16, false, 12, 4, 1>(ctx, p, st, &list);
     else if (pl.np == 16)
         e = pl.x3 ? launch_stream_one<16, true, 12, 4>(ctx, p, st, &list) : launch_stream_one<16, false, 12, 4>(ctx, p, st, &list);
+    else if (p.N <= 24 && !ctx->stream_no_half)
+        e = pl.x3 ? launch_stream_one<32, true, 8, 2, 3>(ctx, p, st, &list) : launch_stream_one<32, false, 8, 2, 3>(ctx, p, st, &list);
     else
         e = pl.x3 ? launch_stream_one<32, true, 8, 2>(ctx, p, st, &list) : launch_stream_one<32, false, 8, 2>(ctx, p, st, &list);
     if (e != cudaSuccess) return fail(ctx, LWC_ERR_INTERNAL, "kernel launch (%s, list of %d) failed: %s", pl.name, list.n, cudaGetErrorString(e));
@@ -429,7 +432,8 @@ int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStr
             e = pl.x3 ? launch_small<16, true>(p, st, ctx->small_kw, ctx->small_u, sr.f16)
                       : launch_small<16, false>(p, st, ctx->small_kw, ctx->small_u, false);
         else if (pl.x3 && sr.f16 && !ctx->small_kw_set && ctx->small_u == 0 && ctx->small_pipe != 0) // the cfg3 route
-            e = ctx->small_pipe == 3 ? launch_small_pipe32<3>(p, st) : launch_small_pipe32<4>(p, st);
+            e = ctx->small_pipe != 3 ? launch_small_pipe32<4>(p, st)
+                                     : (p.N <= 24 && !ctx->stream_no_half ? launch_small_pipe32<3, 3>(p, st) : launch_small_pipe32<3>(p, st));
         else // 32-row pools: 2 warps per request measured best (1.157 vs 1.185 ms at KW=4, cfg3 slice)
             e = pl.x3 ? launch_small<32, true>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u, sr.f16)
                       : launch_small<32, false>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u, false);

@@ -267,7 +267,9 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // lane owns PS private 16-byte slots per (chunk, row group): it issues cp.async for the chunks PS-1 iterations ahead,
 // waits for the oldest group and reads back exactly the bytes it asked for -- no cross-lane synchronisation, no
 // bank conflicts (consecutive lanes, consecutive 16 bytes), and the registers hold one iteration's data only.
-template <int NT, int KW, int U, int PS>
+// NB: 8-row groups (= 8-column MMA tiles) that can hold candidates; NB = 3 serves 17..24-candidate pools without loading,
+// splitting or multiplying the fourth group (10 MMAs per chunk instead of 14).
+template <int NT, int KW, int U, int PS, int NB = NT / 8>
 __device__ __forceinline__ void small_gram_pipe(const ScoreParams &p, int r, float *red, float *fl, float4 *pipe,
                                                 float (&hh)[NT / 16][NT / 8][4], float (&hl)[NT / 16][NT / 8][4]) {
     using C = SmallCfg<NT, true, KW, U>;
@@ -298,7 +300,7 @@ __device__ __forceinline__ void small_gram_pipe(const ScoreParams &p, int r, flo
             for (int u = 0; u < U; ++u) {
                 const int k = (c0 + u) * 16 + 4 * t;
 #pragma unroll
-                for (int q = 0; q < RPL; ++q) {
+                for (int q = 0; q < NB; ++q) {
                     const bool ok = rv[q] && k < D;
                     cp_async16(base + (uint32_t)((u * RPL + q) * 32 * 16), ok ? (const void *)(rowp[q] + (size_t)(c0 + u) * 16) : (const void *)Er,
                                ok ? 16 : 0);
@@ -319,11 +321,16 @@ __device__ __forceinline__ void small_gram_pipe(const ScoreParams &p, int r, flo
         for (int u = 0; u < U; ++u) {
             uint32_t h01[RPL], h23[RPL], l01[RPL], l23[RPL];
 #pragma unroll
-            for (int q = 0; q < RPL; ++q) split_f16x4(slot[(u * RPL + q) * 32], h01[q], h23[q], l01[q], l23[q]);
+            for (int q = 0; q < RPL; ++q) {
+                if (q < NB)
+                    split_f16x4(slot[(u * RPL + q) * 32], h01[q], h23[q], l01[q], l23[q]);
+                else
+                    h01[q] = h23[q] = l01[q] = l23[q] = 0u; // no candidates in these rows
+            }
 #pragma unroll
             for (int a = 0; a < MT; ++a) {
 #pragma unroll
-                for (int b = 0; b < NTL; ++b) {
+                for (int b = 0; b < NB; ++b) {
                     if (b >= 2 * a)
                         mma_m16n8k16_f16(hh[a][b], h01[2 * a], h01[2 * a + 1], h23[2 * a], h23[2 * a + 1], h01[b], h23[b]);
                     mma_m16n8k16_f16(hl[a][b], h01[2 * a], h01[2 * a + 1], h23[2 * a], h23[2 * a + 1], l01[b], l23[b]);
@@ -440,9 +447,10 @@ __device__ __forceinline__ void small_assemble(float *tile, float (&hh)[NT / 16]
 // [2^-12, inf) -- fp16's exponent range was left, or every element underflowed -- is scored again on tf32 pieces by
 // the same CTA (rare: unit-norm or O(1)-norm embeddings never are).
 // PS > 0 (with F16): the loads of the fp16-piece pass are pipelined through PS shared-memory stages (small_gram_pipe).
-template <int NT, bool X3, int KW, int U, bool F16 = false, int PS = 0>
+template <int NT, bool X3, int KW, int U, bool F16 = false, int PS = 0, int NB = NT / 8>
 __global__ void __launch_bounds__(KW * 32, PS > 0 ? 4 : (NT == 16 ? 32 : 16) / KW)
 score_small_kernel(const ScoreParams p) {
+    static_assert(NB == NT / 8 || PS > 0, "fewer row groups: the pipelined pass only");
     static_assert(!F16 || X3, "fp16 pieces are the fp32-grade route");
     static_assert(PS == 0 || F16, "the pipelined loads belong to the fp16-piece pass");
     using C = SmallCfg<NT, X3, KW, U>;
@@ -469,7 +477,7 @@ score_small_kernel(const ScoreParams p) {
 
     if (p.cosine) {
         if (PS > 0)
-            small_gram_pipe<NT, KW, U, (PS > 0 ? PS : 2)>(p, r, red, fl, pipe, hh, hl);
+            small_gram_pipe<NT, KW, U, (PS > 0 ? PS : 2), NB>(p, r, red, fl, pipe, hh, hl);
         else
             small_gram<NT, X3, KW, U, F16>(p, r, red, fl, hh, hl);
         if (warp == 0) small_assemble<NT, X3>(tile, hh, hl, F16 ? kF16LoScale : 1.0f);

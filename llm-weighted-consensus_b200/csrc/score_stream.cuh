@@ -149,7 +149,7 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
     using C = StreamCfg<NT, X3, NCW, NFIN>;
     constexpr int RPL = C::RPL, MT = C::MT, NF = C::NF;
     constexpr int NTL = NB; // column tiles in use (C::NTL of them have room in the park buffer and the S tile)
-    static_assert(NB >= 1 && NB <= C::NTL && (NB == C::NTL || MT == 1), "NB < NT/8 only for one 16-row tile");
+    static_assert(NB >= 1 && NB <= C::NTL && (NB == C::NTL || NB == C::NTL - 1), "NB: the full tile or one 8-row group less");
     constexpr int TPITCH = C::TPITCH, NACC = C::NACC, MAXS = C::MAXS;
 
     extern __shared__ __align__(128) unsigned char smem_raw[];

@@ -474,8 +474,43 @@ def test_pools_of_at_most_eight_take_the_half_tile_form(lwc, oracle, shape, prec
         properties_hold(res[key], V)
 
 
-@pytest.mark.parametrize("shape,prec", [((600, 16, 1536, 4), "fp32"), ((450, 32, 1024, 4), "tf32"), ((300, 9, 772, 3), "fp32"), ((500, 6, 1536, 4), "fp32")],
-                         ids=["cfg2_shape", "n32_tf32", "ragged", "half_tile"])
+@pytest.mark.parametrize("shape", [(700, 24, 3072, 4), (300, 17, 100, 3), (1, 20, 16, 1), (500, 23, 1536, 0), (450, 24, 772, 9)],
+                         ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_pools_of_17_to_24_skip_the_fourth_row_group(lwc, oracle, shape, prec):
+    """17..24 candidates on the 32-row kernels: the fourth 8-row group is neither loaded nor multiplied (NB = 3 in
+    score_small.cuh's pipelined pass and in the ring kernel).  Bit-equal to the full-tile form (LWC_STREAM_HALF=0)."""
+    R, N, D, M = shape
+    p = lwc.PREC_FP32 if prec == "fp32" else lwc.PREC_TF32
+    E, V, w = fast_batch(R, N, D, max(M, 1), seed=900 + N + D)
+    if M == 0:
+        V, w = V[:, :0], w[:, :0]
+    res = {}
+    for half in ("1", "0"):
+        old = os.environ.get("LWC_STREAM_HALF")
+        os.environ["LWC_STREAM_HALF"] = half
+        try:
+            with lwc.Context(device=0) as c:
+                assert c.kernel_for(R, N, D, M, precision=p).startswith("small32_")
+                res[half] = c.score_batch_device(E, V, w, precision=p)
+        finally:
+            if old is None:
+                os.environ.pop("LWC_STREAM_HALF", None)
+            else:
+                os.environ["LWC_STREAM_HALF"] = old
+    for k in res["1"]:
+        assert np.array_equal(res["1"][k], res["0"][k], equal_nan=True), k
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    if prec == "fp32":
+        assert compare(res["1"], want, V) == 1.0
+    else:
+        compare(res["1"], want, V, rtol=TF32_RTOL, atol=1e-5, gap=5e-3, min_agreement=0.95, atol_of_max=TF32_RTOL)
+    properties_hold(res["1"], V)
+
+
+@pytest.mark.parametrize("shape,prec", [((600, 16, 1536, 4), "fp32"), ((450, 32, 1024, 4), "tf32"), ((300, 9, 772, 3), "fp32"), ((500, 6, 1536, 4), "fp32"),
+                                        ((400, 22, 1024, 4), "tf32")],
+                         ids=["cfg2_shape", "n32_tf32", "ragged", "half_tile", "three_groups"])
 def test_a_run_of_same_shaped_batches_is_one_launch_with_the_same_bits(lwc, oracle, shape, prec):
     """lwc_score_batches turns a run of same-shaped ring-kernel batches into ONE launch whose persistent CTAs walk
     the whole run (request g = request g % R of batch g / R).  Launch count, bit-equality with single calls, and
