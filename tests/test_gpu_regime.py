@@ -50,7 +50,8 @@ def fast_batch(R, N, D, M, seed, positive=False):
         V[5] = np.nan          # all voters absent
         E[6, N - 1] = 0.0      # zero-norm candidate
         w[7, 0] = np.nan       # weight None
-        E[8, 1] = E[8, 0]      # duplicate candidates
+        if N > 1:
+            E[8, 1] = E[8, 0]  # duplicate candidates
     return E, V, w
 
 
@@ -587,3 +588,47 @@ def test_cfg3_kernel_load_pipeline_variants(lwc, oracle, stages):
         assert compare(got, want, V) == 1.0
         for k in got:
             assert np.array_equal(got[k], base[k], equal_nan=True), (k, D)
+
+
+# ------------------------------------------------------------------ every route boundary, seeded
+
+def _boundary_shapes():
+    """Pool sizes on both sides of every routing threshold (8 | 9, 16 | 17, 24 | 25, 32 | 33, 64 | 65, 128) crossed with
+    embedding widths that are / are not multiples of 64, 32, 16 and 4, request counts odd and even, above and below one
+    request (or pair) per CTA, and voter counts from 0 to beyond the prefetch window."""
+    rng = np.random.default_rng(20261107)
+    ns = [1, 2, 4, 7, 8, 9, 15, 16, 17, 23, 24, 25, 31, 32, 33, 40, 63, 64, 65, 96, 127, 128]
+    ds = [32, 64, 96, 160, 256, 772, 1000, 1536, 2080]
+    out = []
+    for n in ns:
+        for _ in range(3):
+            d = int(rng.choice(ds))
+            r = int(rng.choice([1, 2, 3, 150, 297, 301]))
+            if n > 32 and d > 1000:
+                r = min(r, 150)
+            m = int(rng.choice([0, 1, 4, 5, 9, 16]))
+            out.append((r, n, d, m))
+    return out
+
+
+@pytest.mark.parametrize("shape", _boundary_shapes(), ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+def test_every_route_boundary_meets_its_bar(ctx, lwc, oracle, shape):
+    R, N, D, M = shape
+    E, V, w = fast_batch(R, N, D, max(M, 1), seed=R + 13 * N + D)
+    # a shared direction per request keeps the cosines positive: with independent gaussian rows at D = 32..64 the
+    # weighted sums cancel (confidences beyond 1) and the 1e-5 bar would be a statement about conditioning, not kernels
+    E += np.float32(0.9) * np.random.default_rng(R + N + D).standard_normal((R, 1, D), dtype=np.float32) * np.abs(E).mean(axis=2, keepdims=True)
+    if R > 8:
+        E[6, N - 1] = 0.0
+    if M == 0:
+        V, w = V[:, :0], w[:, :0]
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    got = ctx.score_batch_device(E, V, w)
+    assert compare(got, want, V) == 1.0, ctx.kernel_for(R, N, D, M)
+    properties_hold(got, V)
+    host = ctx.score_batch(E, V, w)  # few-request path, chunked path: same bits as device-resident
+    for k in got:
+        assert np.array_equal(host[k], got[k], equal_nan=True), (k, ctx.kernel_for(R, N, D, M))
+    fast = ctx.score_batch_device(E, V, w, precision=lwc.PREC_TF32)
+    compare(fast, want, V, rtol=TF32_RTOL, atol=1e-5, gap=5e-3, min_agreement=0.95, atol_of_max=TF32_RTOL)
+    properties_hold(fast, V)
