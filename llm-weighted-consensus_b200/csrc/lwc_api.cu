@@ -77,6 +77,8 @@ struct Plan {
     int np = 0;      // padded pool size
     bool x3 = true;  // small route: compensated 3xTF32
     bool pair = false; // tcgen05 fp32-grade route: two requests of <= 64 candidates per tile
+    size_t req_bytes = 0; // N * D * 4: embeddings of one request
+    int n = 0;            // candidates
     const char *name = "";
 };
 
@@ -95,6 +97,8 @@ Plan plan_for(const lwc_batch_desc &d, const void *E) {
         return pl;
     }
     const bool aligned = (d.D % 4 == 0) && ((reinterpret_cast<uintptr_t>(E) & 15u) == 0);
+    pl.req_bytes = (size_t)d.N * d.D * 4;
+    pl.n = d.N;
     if (d.N <= 32 && aligned) {
         pl.route = ROUTE_SMALL;
         pl.np = d.N <= 16 ? 16 : 32;
@@ -309,8 +313,12 @@ cudaError_t ensure_fix_flags(lwc_ctx *ctx, int R) {
 template <int NT, bool X3, int NCW, int NF, int NB = NT / 8>
 cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st, const lwc::ScoreList *list = nullptr) {
     using C = lwc::StreamCfg<NT, X3, NCW, NF>;
-    const size_t avail = (size_t)ctx->max_smem_optin - 128 - C::fixed_bytes();
     lwc::StreamGeom geo;
+    // LWC_STREAM_PARKS=2: a second park buffer, so that the consumers hand request q over while a finaliser is still
+    // draining q - 1.  Built because ncu at 16 x 384 showed 18 % of all stall samples on that one wait; measured: no
+    // change at any width (256..1024) -- the wait is where the consumers idle, not why.  Default 1.
+    geo.parks = ctx->stream_parks == 2 ? 2 : 1;
+    const size_t avail = (size_t)ctx->max_smem_optin - 128 - C::fixed_bytes(geo.parks);
     // stage width: 3 KB per row copy is where the bulk-copy engine reaches HBM speed
     // (profiles/r1_tma_probe.txt); shrink it until at least 3 stages fit.
     const int dpad = (p.D + 15) / 16 * 16;
@@ -339,7 +347,7 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(C::THREADS);
-    cfg.dynamicSmemBytes = C::smem_bytes(geo.ks, geo.stages, rows);
+    cfg.dynamicSmemBytes = C::smem_bytes(geo.ks, geo.stages, rows, geo.parks);
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; // pairs with griddepcontrol.* in the kernel
@@ -368,6 +376,8 @@ cudaError_t launch_stream(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t 
         case 86: return launch_stream_one<NT, X3, 8, 6>(ctx, p, st);
         case 122: return launch_stream_one<NT, X3, 12, 2>(ctx, p, st);
         case 124: return launch_stream_one<NT, X3, 12, 4>(ctx, p, st);
+        case 126: return launch_stream_one<NT, X3, 12, 6>(ctx, p, st);
+        case 128: return launch_stream_one<NT, X3, 12, 8>(ctx, p, st);
         default: return launch_stream_one<NT, X3, 8, 2>(ctx, p, st);
     }
 }
@@ -378,6 +388,8 @@ cudaError_t launch_stream(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t 
 //   consumer warps became issue-bound on the piece arithmetic) and dropped.
 //   direct kernel (score_small): fp32-grade 32-row pools by default, and everything under LWC_SMALL_IMPL=direct;
 //   fp16 pieces with an inline tf32 fallback (LWC_SMALL_X3=tf32: tf32 pieces only).
+constexpr size_t kDirectBelowBytes = (size_t)56 << 10, kDirectBelowBytesTf32 = (size_t)40 << 10, kDirectBelowBytes8 = (size_t)20 << 10,
+                 kDirectBelowBytes32 = (size_t)72 << 10;
 struct SmallRoute {
     bool stream; // persistent ring kernel, else one CTA per request
     bool f16;    // fp32-grade Gram on fp16 pieces
@@ -389,8 +401,16 @@ SmallRoute small_route(const lwc_ctx *ctx, const Plan &pl) {
         r.stream = false;
     else if (ctx->force_stream)
         r.stream = true;
+    else if (pl.np == 32 && pl.x3)
+        r.stream = false; // 32-row fp32-grade pools: the direct kernel is faster on either kind of pieces
     else
-        r.stream = !(pl.np == 32 && pl.x3); // 32-row fp32-grade pools: the direct kernel is faster on either kind of pieces
+        // Small requests: the ring kernel pays ~1.1 us per request whatever its size (every consumer warp meets every
+        // stage, parks, a finaliser drains), the direct kernel a CTA launch.  Measured crossover (profiles/
+        // r2_width_sweep.jsonl): 16 x 384 runs at 0.78 of HBM direct against 0.49 on the ring, 16 x 768 at 0.86 / 0.82,
+        // 16 x 1536 (cfg2) at 0.93 / 1.00.  LWC_SMALL_IMPL=stream keeps the ring for everything.
+        // Pools of at most 8 candidates keep the ring down to 20 KB (its half-tile form does half the work per byte;
+        // 8 x 1024 runs at 0.74 there against 0.61 direct), single-pass TF32 down to 40 KB (16 x 768: 1.00 / 0.96).
+        r.stream = pl.req_bytes > (pl.n <= 8 ? kDirectBelowBytes8 : (pl.np == 32 ? kDirectBelowBytes32 : (pl.x3 ? kDirectBelowBytes : kDirectBelowBytesTf32)));
     r.f16 = f16_ok && !r.stream;
     return r;
 }
@@ -429,8 +449,9 @@ int launch_plan(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, cudaStr
             e = pl.x3 ? launch_stream<32, true>(ctx, p, st) : launch_stream<32, false>(ctx, p, st);
     } else if (pl.route == ROUTE_SMALL) {
         if (pl.np == 16)
-            e = pl.x3 ? launch_small<16, true>(p, st, ctx->small_kw, ctx->small_u, sr.f16)
-                      : launch_small<16, false>(p, st, ctx->small_kw, ctx->small_u, false);
+            // (2 warps per request: 16 x 384 at 0.78 of HBM against 0.60 with 4)
+            e = pl.x3 ? launch_small<16, true>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u, sr.f16)
+                      : launch_small<16, false>(p, st, ctx->small_kw_set ? ctx->small_kw : 2, ctx->small_u, false);
         else if (pl.x3 && sr.f16 && !ctx->small_kw_set && ctx->small_u == 0 && ctx->small_pipe != 0) // the cfg3 route
             e = ctx->small_pipe != 3 ? launch_small_pipe32<4>(p, st)
                                      : (p.N <= 24 && !ctx->stream_no_half ? launch_small_pipe32<3, 3>(p, st) : launch_small_pipe32<3>(p, st));
@@ -709,6 +730,7 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     if (const char *s = getenv("LWC_STREAM_NCW")) ctx->stream_ncw = atoi(s);
     if (const char *s = getenv("LWC_STREAM_KC")) ctx->stream_kc = atoi(s);
     if (const char *s = getenv("LWC_STREAM_SLOTS")) ctx->stream_slots = atoi(s);
+    if (const char *s = getenv("LWC_STREAM_PARKS")) ctx->stream_parks = (atoi(s) == 1 || atoi(s) == 2) ? atoi(s) : 0;
     if (const char *s = getenv("LWC_STREAM_NF")) ctx->stream_nf = atoi(s);
     if (const char *s = getenv("LWC_POOL_NO_P2P")) ctx->no_p2p = atoi(s);
     if (const char *s = getenv("LWC_CHUNK_REQUESTS")) ctx->chunk_requests = atoi(s);

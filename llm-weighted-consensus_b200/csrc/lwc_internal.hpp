@@ -75,6 +75,7 @@ struct lwc_ctx {
     size_t tc_flags_cap = 0;
     int small_pipe = 3;        // LWC_SMALL_PIPE=0|3|4: shared-memory load pipeline stages of the 32-row fp16-piece kernel (0: register loads)
     int small_x3_tf32 = 0;     // LWC_SMALL_X3=tf32: the one-CTA-per-request fp32-grade kernel on tf32 pieces
+    int stream_parks = 0;      // LWC_STREAM_PARKS=1|2: park buffers of the ring kernel (0: by request size)
     int stream_no_half = 0;    // LWC_STREAM_HALF=0: pools of <= 8 candidates on the full 16-row tile of the ring kernel
     int tc_no_pair = 0;        // LWC_TC_PAIR=0: pools of <= 64 candidates one to a tile (score_tc16_kernel<false>)
     int tc_x3_tf32 = 0;        // LWC_TC_X3=tf32: fp32-grade large pools on tf32 pieces (score_tc_kernel<true>) only

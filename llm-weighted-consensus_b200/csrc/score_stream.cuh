@@ -96,6 +96,7 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
 struct StreamGeom {
     int ks;     // columns per stage (multiple of 16)
     int stages; // ring depth
+    int parks;  // park buffers (1 or 2): 2 lets the consumers park request q while a finaliser still drains q - 1
 };
 
 template <int NT, bool X3, int NCW, int NFIN>
@@ -108,11 +109,11 @@ struct StreamCfg {
     static constexpr int THREADS = (1 + NCW + NF) * 32;
     static constexpr size_t RED_BYTES = (size_t)NCW * NACC * 32 * sizeof(float);
     static constexpr size_t TILE_BYTES = (size_t)NF * NT * TPITCH * sizeof(float);
-    static constexpr size_t BAR_BYTES = (size_t)(2 * MAXS + 2 + NF) * sizeof(uint64_t);
-    static constexpr size_t fixed_bytes() { return RED_BYTES + TILE_BYTES + BAR_BYTES + 128; }
+    static constexpr size_t BAR_BYTES = (size_t)(2 * MAXS + 4 + NF) * sizeof(uint64_t);
+    static constexpr size_t fixed_bytes(int parks = 1) { return (size_t)parks * RED_BYTES + TILE_BYTES + BAR_BYTES + 128; }
     // rows: candidate rows a stage has room for (NT, or 8 in the half-tile form: twice the stages, twice the bytes in flight)
     static constexpr size_t stage_bytes(int ks, int rows = NT) { return (size_t)rows * (ks * sizeof(float) + 64); }
-    static constexpr size_t smem_bytes(int ks, int stages, int rows = NT) { return fixed_bytes() + (size_t)stages * stage_bytes(ks, rows); }
+    static constexpr size_t smem_bytes(int ks, int stages, int rows = NT, int parks = 1) { return fixed_bytes(parks) + (size_t)stages * stage_bytes(ks, rows); }
 };
 
 constexpr bool kStreamFlush = kMmaChain < (1 << 20); // A/B builds (-DLWC_MMA_CHAIN=1000000) compile the flush out
@@ -158,11 +159,12 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
     constexpr int SROWS = NB * 8;        // candidate rows a stage holds
     const int stageb = SROWS * pitchb;   // bytes per stage
     unsigned char *ring = smem_raw;                                    // [S][SROWS][pitchb]
-    float *red = reinterpret_cast<float *>(ring + (size_t)S * stageb); // [NCW][NACC][32]
-    float *tiles = red + (size_t)NCW * NACC * 32;                      // [NF][NT][TPITCH]
+    const int P = geo.parks;                                           // park buffers: request q uses buffer q % P
+    float *red = reinterpret_cast<float *>(ring + (size_t)S * stageb); // [P][NCW][NACC][32]
+    float *tiles = red + (size_t)P * NCW * NACC * 32;                  // [NF][NT][TPITCH]
     uint64_t *bars = reinterpret_cast<uint64_t *>(tiles + (size_t)NF * NT * TPITCH);
     const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * MAXS;
-    const uint32_t redfull = empty0 + 8 * MAXS, redempty = redfull + 8, turn0 = redempty + 8;
+    const uint32_t redfull0 = empty0 + 8 * MAXS, redempty0 = redfull0 + 16, turn0 = redempty0 + 16; // [2] each
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int N = p.N, D = p.D, M = p.M;
@@ -183,8 +185,10 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
             mbar_init(full0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, NCW);
         }
-        mbar_init(redfull, NCW);
-        mbar_init(redempty, 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(redfull0 + 8 * b, NCW);
+            mbar_init(redempty0 + 8 * b, 1);
+        }
         for (int b = 0; b < NF; ++b) mbar_init(turn0 + 8 * b, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -335,9 +339,11 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
                         }
             }
             // ---- request end: park this warp's partial fragments (buffer free once q-1 was drained)
-            mbar_wait(redempty, ((uint32_t)q & 1u) ^ 1u);
+            const int pb = P == 2 ? (q & 1) : 0;       // park buffer of this request
+            const uint32_t pk = (uint32_t)(P == 2 ? q >> 1 : q); // its use count
+            mbar_wait(redempty0 + 8 * pb, (pk & 1u) ^ 1u);
             {
-                float *dst = red + (size_t)cw * NACC * 32 + lane;
+                float *dst = red + ((size_t)pb * NCW + cw) * NACC * 32 + lane;
                 int k = 0;
 #pragma unroll
                 for (int a = 0; a < MT; ++a)
@@ -352,7 +358,7 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
                         }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(redfull);
+            if (lane == 0) mbar_arrive(redfull0 + 8 * pb);
         }
         return;
     }
@@ -382,7 +388,10 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
         // wait for the token: the owner of q-1 has drained the park buffer, so the park barrier is
         // exactly in phase q (this warp did not watch the phases in between)
         if (q > 0) mbar_wait(turn0 + 8 * f, (uint32_t)(f == 0 ? k - 1 : k) & 1u);
-        mbar_wait(redfull, (uint32_t)q & 1u);
+        // (two park buffers: buffer q % 2 was last drained by the owner of q - 2, before the token got here, and cannot
+        // fill for q + 2 until this warp has drained it -- its barrier is exactly in use q / 2)
+        const int pb = P == 2 ? (q & 1) : 0;
+        mbar_wait(redfull0 + 8 * pb, (uint32_t)(P == 2 ? q >> 1 : q) & 1u);
         const int r = r_begin + q;
         float sh[MT][NTL][4], sl[MT][NTL][4];
 #pragma unroll
@@ -392,7 +401,7 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
 #pragma unroll
                 for (int e = 0; e < 4; ++e) sh[a][b][e] = sl[a][b][e] = 0.f;
         for (int ws = 0; ws < NCW; ++ws) { // consumer order: timing-independent sums
-            const float *src = red + (size_t)ws * NACC * 32 + lane;
+            const float *src = red + ((size_t)pb * NCW + ws) * NACC * 32 + lane;
             int k = 0;
 #pragma unroll
             for (int a = 0; a < MT; ++a)
@@ -406,7 +415,7 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
         }
         __syncwarp();
         if (lane == 0) {
-            mbar_arrive(redempty); // partials are in registers: consumers may park again
+            mbar_arrive(redempty0 + 8 * pb); // partials are in registers: consumers may park again
             if (q + 1 < nreq) mbar_arrive(turn0 + 8 * ((f + 1) % NF)); // pass the token
         }
 

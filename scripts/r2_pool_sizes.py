@@ -1,5 +1,6 @@
 """Kernel-only sweep over candidate-pool sizes between the BASELINE shapes (device-resident inputs, one launch per batch,
-CUDA events): where each route stands against the measured HBM peak when the pool does not fill its tile."""
+CUDA events): where each route stands against the measured HBM peak when the pool does not fill its tile.
+   usage: r2_pool_sizes.py [N,N,...] [voters] [D]"""
 import json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 for p in (ROOT, os.path.join(ROOT, "llm-weighted-consensus_b200")):
@@ -12,7 +13,7 @@ from lwc_b200 import synth
 def main():
     torch.cuda.set_device(0)
     peak, _ = bench.load_peaks()
-    D, M = 3072, int(sys.argv[2]) if len(sys.argv) > 2 else 8
+    D, M = int(sys.argv[3]) if len(sys.argv) > 3 else 3072, int(sys.argv[2]) if len(sys.argv) > 2 else 8
     sizes = [int(x) for x in (sys.argv[1].split(",") if len(sys.argv) > 1 else "8,16,24,32,40,48,64,80,96,128".split(","))]
     for N in sizes:
         R = max(256, int(1.6e9 / (N * D * 4)))

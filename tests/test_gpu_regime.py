@@ -8,6 +8,7 @@ accumulator hand-offs per request -- including an ODD chunk count, where the acc
 alternates from request to request.  Checker: the f64 oracle on every request (tally semantics
 src/score/completions/client.rs:410-449; tolerances of SURVEY.md 8.0).
 """
+import contextlib
 import os
 
 import numpy as np
@@ -32,6 +33,25 @@ def ctx(lwc):
     c = lwc.Context(device=0)
     yield c
     c.close()
+
+
+@contextlib.contextmanager
+def env(**kv):
+    """Environment knobs are read once per context: set them around the lwc.Context(...) they are meant for."""
+    old = {k: os.environ.get(k) for k in kv}
+    try:
+        for k, v in kv.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+        yield
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
 
 
 def fast_batch(R, N, D, M, seed, positive=False):
@@ -450,8 +470,9 @@ def test_pools_of_at_most_eight_take_the_half_tile_form(lwc, oracle, shape, prec
     # the half-tile form streams wider stages by default (6 KB row copies), which deals the columns to the consumer
     # warps differently; at one stage width the two forms add the same terms in the same order
     for half, kc in (("1", "768"), ("0", "768"), ("1", None)):
-        old = {k: os.environ.get(k) for k in ("LWC_STREAM_HALF", "LWC_STREAM_KC")}
+        old = {k: os.environ.get(k) for k in ("LWC_STREAM_HALF", "LWC_STREAM_KC", "LWC_SMALL_IMPL")}
         os.environ["LWC_STREAM_HALF"] = half
+        os.environ["LWC_SMALL_IMPL"] = "stream"  # requests under 56 KB go to the one-CTA-per-request kernel by default
         if kc:
             os.environ["LWC_STREAM_KC"] = kc
         try:
@@ -524,7 +545,8 @@ def test_a_run_of_same_shaped_batches_is_one_launch_with_the_same_bits(lwc, orac
         old = os.environ.get("LWC_LIST_FUSION")
         os.environ["LWC_LIST_FUSION"] = fusion
         try:
-            with lwc.Context(device=0, flags=lwc.CTX_INPUTS_RESIDENT) as c:
+            # (the ring kernel also for the two shapes under 56 KB per request, which default to one CTA per request)
+            with env(LWC_SMALL_IMPL="stream"), lwc.Context(device=0, flags=lwc.CTX_INPUTS_RESIDENT) as c:
                 singles = [c.score_batch_device(E, V, w, precision=p) for E, V, w in batches]
                 keep, ptrs = [], {k: [] for k in ("E", "V", "w", "conf", "cw", "agree", "winner", "rank")}
                 for E, V, w in batches:
