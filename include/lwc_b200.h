@@ -183,7 +183,8 @@ int32_t lwc_stage_f64_bf16(lwc_ctx *ctx, const double *src, size_t n, uint16_t *
  * entry of one, may be NULL).  Every batch must be LWC_MEM_DEVICE.  The list is validated before the first
  * launch: a 400 means nothing was enqueued.  Results are bit-identical to n_batches single calls.  What
  * changes: (1) one lock, one argument check and one library call per list instead of per batch; (2) a RUN
- * of consecutive entries with the same descriptor that take the small-pool ring kernel (N <= 32, cosine)
+ * of consecutive entries with the same descriptor that take the small-pool ring kernel (N <= 32, cosine,
+ * more than 56 KB of embeddings per request -- smaller requests run one CTA each and launch batch by batch)
  * is scored by ONE launch per 32 batches -- its persistent CTAs walk the whole run, so launch latency, the
  * first bytes' latency and the last requests' tail are paid once per run instead of once per batch, and
  * nothing depends on the host staying a launch ahead of a ~60 us kernel (cfg2: 63.1 us per batch = 0.99 of
