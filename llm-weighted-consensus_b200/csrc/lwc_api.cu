@@ -410,7 +410,9 @@ SmallRoute small_route(const lwc_ctx *ctx, const Plan &pl) {
         // 16 x 1536 (cfg2) at 0.93 / 1.00.  LWC_SMALL_IMPL=stream keeps the ring for everything.
         // Pools of at most 8 candidates keep the ring down to 20 KB (its half-tile form does half the work per byte;
         // 8 x 1024 runs at 0.74 there against 0.61 direct), single-pass TF32 down to 40 KB (16 x 768: 1.00 / 0.96).
-        r.stream = pl.req_bytes > (pl.n <= 8 ? kDirectBelowBytes8 : (pl.np == 32 ? kDirectBelowBytes32 : (pl.x3 ? kDirectBelowBytes : kDirectBelowBytesTf32)));
+        // 9..12 candidates, fp32-grade: the ring does a full 16-row tile's work for them at any width (10 x 1536: 0.63 of
+        // HBM, compute-bound like 16 x 1536) -- direct at every size (0.75-0.77; 12: 0.80-0.85 against 0.75-0.84).
+        r.stream = !(pl.x3 && pl.n >= 9 && pl.n <= 12) && pl.req_bytes > (pl.n <= 8 ? kDirectBelowBytes8 : (pl.np == 32 ? kDirectBelowBytes32 : (pl.x3 ? kDirectBelowBytes : kDirectBelowBytesTf32)));
     r.f16 = f16_ok && !r.stream;
     return r;
 }
