@@ -16,6 +16,7 @@
 #include "score_stream.cuh"
 #include "score_tc.cuh"
 #include "score_tc16.cuh"
+#include "score_tc16a.cuh"
 #include "convert.cuh"
 #include "vote_kernel.cuh"
 
@@ -273,6 +274,10 @@ cudaError_t launch_tc16(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st
         cudaError_t e = cudaFuncSetAttribute(lwc::score_tc16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(lwc::score_tc16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(lwc::score_tc16a_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(lwc::score_tc16a_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
         if (e != cudaSuccess) return e;
         configured[ctx->device & 63] = true;
     }
@@ -285,7 +290,13 @@ cudaError_t launch_tc16(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st
         return cudaErrorInvalidValue;
     const int ntiles = pair ? (p.R + 1) / 2 : p.R;
     const int grid = ntiles < ctx->sm_count ? ntiles : ctx->sm_count;
-    if (pair)
+    // LWC_TC16_A=tmem: the A operand in tensor memory (score_tc16a.cuh); smem: both operands in shared memory
+    if (ctx->tc16_a_tmem) {
+        if (pair)
+            lwc::score_tc16a_kernel<true><<<grid, lwc::kT16aThreads, lwc::tc16_smem_bytes(geo.stages), st>>>(tm, p, geo, static_cast<int *>(ctx->tc_flags));
+        else
+            lwc::score_tc16a_kernel<false><<<grid, lwc::kT16aThreads, lwc::tc16_smem_bytes(geo.stages), st>>>(tm, p, geo, static_cast<int *>(ctx->tc_flags));
+    } else if (pair)
         lwc::score_tc16_kernel<true><<<grid, lwc::kT16Threads, lwc::tc16_smem_bytes(geo.stages), st>>>(tm, p, geo, static_cast<int *>(ctx->tc_flags));
     else
         lwc::score_tc16_kernel<false><<<grid, lwc::kT16Threads, lwc::tc16_smem_bytes(geo.stages), st>>>(tm, p, geo, static_cast<int *>(ctx->tc_flags));
@@ -740,6 +751,7 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     if (const char *s = getenv("LWC_TC_KO")) ctx->tc_ko = atoi(s);
     if (const char *s = getenv("LWC_TC_X3")) ctx->tc_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_TC_PAIR")) ctx->tc_no_pair = atoi(s) == 0 ? 1 : 0;
+    if (const char *s = getenv("LWC_TC16_A")) ctx->tc16_a_tmem = strcmp(s, "tmem") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_STREAM_HALF")) ctx->stream_no_half = atoi(s) == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_X3")) ctx->small_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_PIPE")) ctx->small_pipe = atoi(s);

@@ -77,6 +77,7 @@ struct lwc_ctx {
     int small_x3_tf32 = 0;     // LWC_SMALL_X3=tf32: the one-CTA-per-request fp32-grade kernel on tf32 pieces
     int stream_parks = 0;      // LWC_STREAM_PARKS=1|2: park buffers of the ring kernel (0: by request size)
     int stream_no_half = 0;    // LWC_STREAM_HALF=0: pools of <= 8 candidates on the full 16-row tile of the ring kernel
+    int tc16_a_tmem = 1;       // LWC_TC16_A=tmem|smem: fp32-grade tcgen05 route with the A operand in tensor memory (score_tc16a.cuh)
     int tc_no_pair = 0;        // LWC_TC_PAIR=0: pools of <= 64 candidates one to a tile (score_tc16_kernel<false>)
     int tc_x3_tf32 = 0;        // LWC_TC_X3=tf32: fp32-grade large pools on tf32 pieces (score_tc_kernel<true>) only
     int tc_ko = 0;     // operand slabs per stage of the tcgen05 kernel (LWC_TC_KO)

@@ -654,3 +654,24 @@ def test_every_route_boundary_meets_its_bar(ctx, lwc, oracle, shape):
     fast = ctx.score_batch_device(E, V, w, precision=lwc.PREC_TF32)
     compare(fast, want, V, rtol=TF32_RTOL, atol=1e-5, gap=5e-3, min_agreement=0.95, atol_of_max=TF32_RTOL)
     properties_hold(fast, V)
+
+
+@pytest.mark.parametrize("shape", [(600, 128, 3072, 16), (301, 100, 2336, 5), (333, 57, 1024, 3), (2, 64, 96, 16)],
+                         ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+def test_operand_a_in_tensor_memory_and_in_shared_memory_agree(lwc, oracle, shape):
+    """The fp32-grade tcgen05 route takes its A operand (the h tile) from TMEM by default (score_tc16a.cuh: the transform
+    warps store it there, one thread per row) and from shared memory under LWC_TC16_A=smem (score_tc16.cuh).  Same pieces,
+    same X chunks; Y runs through one accumulator instead of two, so the last bits may differ -- both meet the bar."""
+    R, N, D, M = shape
+    E, V, w = fast_batch(R, N, D, M, seed=1200 + N + D)
+    if R > 8:
+        E[3] *= np.float32(1e-6)  # marked: the fix-up pass rewrites it on either route
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    res = {}
+    for a in ("tmem", "smem"):
+        with env(LWC_TC16_A=a), lwc.Context(device=0) as c:
+            res[a] = c.score_batch_device(E, V, w)
+            assert compare(res[a], want, V) == 1.0, a
+            properties_hold(res[a], V)
+    assert np.array_equal(res["tmem"]["winner"], res["smem"]["winner"])
+    np.testing.assert_allclose(res["tmem"]["conf"], res["smem"]["conf"], rtol=2e-5, atol=2e-7)  # each within 1e-5 + 1e-7 of the oracle
