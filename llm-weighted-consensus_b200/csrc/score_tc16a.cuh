@@ -1,24 +1,25 @@
-// score_tc16a.cuh -- score_tc16_kernel with the A operand in tensor memory, sm_100a.
+// score_tc16a.cuh -- score_tc16_kernel with the A operands in tensor memory, sm_100a.
 //
 // score_tc16_kernel (score_tc16.cuh) is bound by the shared-memory pipe: per 32 KB of HBM traffic it moves 144 KB
-// through shared memory, 48 KB of them the tensor core reading its operands -- A = the h tile (16 KB) and B = [h ; l]
-// (32 KB), although A is the first half of B.  tcgen05.mma can take A from TMEM instead.  Here the transform warps, which
-// hold every h value in registers anyway, also store it into a ring of four A tiles in TMEM (tcgen05.st: no
-// shared-memory traffic), and the issuer runs two half-width MMAs per K step with A from TMEM:
-//     X (+)= h h^T   (B = the h tile in shared memory)        Y (+)= h l^T   (B = the l tile)
-// 128 KB per unit instead of 144.  TMEM (512 columns): X0 | X1 (double-buffered per chunk, as before) | Y (ONE
-// accumulator for the whole request: the next request's first MMA waits until the epilogue has read it) | 4 x 32
-// columns of A tiles.  To store a row of h a thread must own that row's TMEM lane, so the transform is one thread per
-// row (warps 2, 3, 8, 9 have warp % 4 = 2, 3, 0, 1: the four lane quarters); its output footprint is still exactly its
-// input footprint.  Everything else -- pieces, range check and fix-up pass, chunked X, PAIR mode, epilogue arithmetic --
-// is score_tc16.cuh's.
-// Measured (same box, scripts/r2_ab_tc16.sh form): cfg4 2.525 -> 2.485 ms (0.796 -> 0.808 of HBM); 1.6 GB launches:
-// 128 candidates 0.778 -> 0.814, two 64-candidate requests per tile 0.838 -> 0.868; ncu on the 2,048-request slice
-// 646 -> 601 us, 3.254 GB DRAM read, arbitration conflicts on the LSU's shared-memory wavefronts 23 M -> 11 M
-// (profiles/r2_tc16a_raw.csv).  Less than the 11 % of shared-memory traffic it removes: the pipe is shared with the
-// TMA writes and the B reads whatever A does.  Tried and dropped (LWC_T16A_SETS=2): a second set of four transform
-// warps taking the odd units -- no gain with two requests per tile (0.864), and at 448 threads the 128-register cap
-// spills the one-request epilogue (2.75 ms).
+// through shared memory -- 32 KB TMA in, 32 + 32 KB transform, 16 + 32 KB operand reads (A = the h tile, B = [h ; l]).
+// tcgen05.mma can take A from TMEM instead, and S = X + 2^-11 (Y + Y^T) does not care whether Y is h l^T or its
+// transpose l h^T.  So here BOTH pieces go to TMEM as A operands and only h stays in shared memory, as the one B tile:
+//     X (+)= h h^T   (A = h from TMEM, B = the h tile)        Y (+)= l h^T   (A = l from TMEM, B = the h tile)
+// The transform warps hold every h and l value in registers anyway: they store the row of h into shared memory (16 KB
+// per unit instead of 32) and both rows into a ring of two [h | l] tile pairs in TMEM (tcgen05.st: no shared-memory
+// traffic).  112 KB per unit instead of 144.  TMEM (512 columns): X0 | X1 (double-buffered per chunk, as before) | Y
+// (ONE accumulator for the whole request: the next request's first MMA waits until the epilogue has read it) | 2 x
+// (32 + 32) columns of A tiles.  To store a row a thread must own that row's TMEM lane, so the transform is one thread
+// per row (warps 2, 3, 8, 9 have warp % 4 = 2, 3, 0, 1: the four lane quarters); it overwrites its own row of slab 0 with
+// the row of the h tile, slab 1 is left behind.  Everything else -- pieces, range check and fix-up pass, chunked X, PAIR
+// mode, epilogue arithmetic -- is score_tc16.cuh's.
+// Measured (same box, LWC_TC16_A=smem against the default): cfg4 2.422 -> 2.349 ms (0.830 -> 0.856 of HBM); 1.6 GB
+// launches: 128 candidates 0.802 -> 0.852, two 64-candidate requests per tile 0.875 -> 0.927, two 48-candidate 0.727 ->
+// 0.762.  With only h moved to TMEM (l still a second B tile in shared memory, 128 KB per unit) the steps were 2.525 ->
+// 2.485 ms, 0.778 -> 0.814, 0.838 -> 0.868; ncu on the 2,048-request slice of that form: 646 -> 601 us, arbitration
+// conflicts on the LSU's shared-memory wavefronts 23 M -> 11 M (profiles/r2_tc16a_raw.csv).  Tried and dropped
+// (LWC_T16A_SETS=2): a second set of four transform warps taking the odd units -- no gain with two requests per tile, and
+// at 448 threads the 128-register cap spills the one-request epilogue (2.75 ms).
 #pragma once
 
 #include "score_tc16.cuh"
@@ -26,7 +27,7 @@
 namespace lwc {
 
 constexpr uint32_t kT16aCol = 384;  // first TMEM column of the A tiles
-constexpr uint32_t kT16aTiles = 4;  // A tiles in flight (32 columns each)
+constexpr uint32_t kT16aTiles = 2;  // A tile pairs in flight: [h | l] of one unit, 32 + 32 columns
 #ifndef LWC_T16A_SETS
 #define LWC_T16A_SETS 1
 #endif
@@ -143,13 +144,12 @@ score_tc16a_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p,
                     mbar_wait_backoff(ready0 + 8 * slot, phase, kT16BackoffM); // the stage holds [h ; l], TMEM holds h
                     tc_fence_after();
                     const uint32_t unit = ring_u32 + slot * kT16UnitBytes;
-                    const uint32_t a_tmem = tmem_base + kT16aCol + (unit_no % kT16aTiles) * 32u;
+                    const uint32_t a_tmem = tmem_base + kT16aCol + (unit_no % kT16aTiles) * 64u;
 #pragma unroll
                     for (int kk = 0; kk < 4; ++kk) { // 4 x K = 16: 8 TMEM columns of A, 32 bytes inside the swizzle atom of B
-                        umma_f16_ts(x_tmem, a_tmem + kk * 8u, umma_desc_sw128(unit + kk * 32), idesc,
-                                    (kk == 0 && chunk_start) ? 0u : 1u);                                   // X (+)= h h^T
-                        umma_f16_ts(tmem_base + 256u, a_tmem + kk * 8u, umma_desc_sw128(unit + kTcSlabBytes + kk * 32), idesc,
-                                    (kk == 0 && u == 0) ? 0u : 1u);                                        // Y (+)= h l^T
+                        const uint64_t bh = umma_desc_sw128(unit + kk * 32); // B is the h tile for both products
+                        umma_f16_ts(x_tmem, a_tmem + kk * 8u, bh, idesc, (kk == 0 && chunk_start) ? 0u : 1u);          // X (+)= h h^T
+                        umma_f16_ts(tmem_base + 256u, a_tmem + 32u + kk * 8u, bh, idesc, (kk == 0 && u == 0) ? 0u : 1u); // Y (+)= l h^T
                     }
                     umma_commit(empty0 + 8 * slot); // the stage's smem AND its A tile are free once these MMAs are done
                     if (++slot == S) {
@@ -164,11 +164,11 @@ score_tc16a_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p,
         __syncwarp();
     } else if (warp == 2 || warp == 3 || warp >= 8) {
         // ===================== transform, in place, one thread per row =====================
-        // fp32 slabs -> [h ; l] fp16 tiles in shared memory (the B operands) AND h into this unit's A tile in TMEM.
+        // fp32 slabs -> the h tile in shared memory (the B operand) and the rows of h and l into this unit's A tiles in TMEM.
         // Thread t of the warp with warp % 4 == g owns row 32g + t: tcgen05.st lets a warp reach exactly that quarter of
         // the lanes, and a thread its own lane.  The row's 2 x 128 bytes are read completely (16 x 128-bit loads: the
         // 16-byte chunks of 8 consecutive rows are XOR-swizzled onto 8 different bank groups, so a quarter-warp is
-        // conflict-free), converted, and written back over themselves as the row of the h tile and the row of the l tile.
+        // conflict-free), converted, and the row of slab 0 is overwritten with the row of the h tile.
         const int tset = warp >= 10 ? 1 : 0; // which units this warp takes: unit_no % kT16aSets == tset
         const int row = 32 * (warp & 3) + lane;
         const bool on = (PAIR ? (row & 63) : row) < N; // rows past the pool arrive zero-filled: zero pieces, nothing to do
@@ -189,9 +189,9 @@ score_tc16a_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p,
                 }
                 mbar_wait_backoff(full0 + 8 * slot, phase, kT16BackoffT);
                 const uint32_t r0 = smem_u32(ring) + (uint32_t)slot * kT16UnitBytes + (uint32_t)row * 128u, r1 = r0 + (uint32_t)kTcSlabBytes;
-                uint32_t hreg[32];
+                uint32_t hreg[32], lreg[32];
 #pragma unroll
-                for (int e = 0; e < 32; ++e) hreg[e] = 0u;
+                for (int e = 0; e < 32; ++e) hreg[e] = lreg[e] = 0u;
                 if (on) {
                     float4 x[16];
 #pragma unroll
@@ -207,8 +207,8 @@ score_tc16a_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p,
                         const uint32_t o0 = (((uint32_t)j ^ sw) << 4), o1 = (((uint32_t)(4 + j) ^ sw) << 4);
                         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(r0 + o0), "r"(h0.x), "r"(h0.y), "r"(h0.z), "r"(h0.w) : "memory");
                         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(r0 + o1), "r"(h1.x), "r"(h1.y), "r"(h1.z), "r"(h1.w) : "memory");
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(r1 + o0), "r"(l0.x), "r"(l0.y), "r"(l0.z), "r"(l0.w) : "memory");
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(r1 + o1), "r"(l1.x), "r"(l1.y), "r"(l1.z), "r"(l1.w) : "memory");
+                        lreg[4 * j] = l0.x, lreg[4 * j + 1] = l0.y, lreg[4 * j + 2] = l0.z, lreg[4 * j + 3] = l0.w;
+                        lreg[16 + 4 * j] = l1.x, lreg[16 + 4 * j + 1] = l1.y, lreg[16 + 4 * j + 2] = l1.z, lreg[16 + 4 * j + 3] = l1.w;
                         hreg[4 * j] = h0.x, hreg[4 * j + 1] = h0.y, hreg[4 * j + 2] = h0.z, hreg[4 * j + 3] = h0.w;
                         hreg[16 + 4 * j] = h1.x, hreg[16 + 4 * j + 1] = h1.y, hreg[16 + 4 * j + 2] = h1.z, hreg[16 + 4 * j + 3] = h1.w;
                     }
@@ -221,7 +221,8 @@ score_tc16a_kernel(const __grid_constant__ CUtensorMap tmE, const ScoreParams p,
                         phase_a ^= 1u;
                     }
                 }
-                tmem_st32(tmem_base + lane_taddr + (unit_no % kT16aTiles) * 32u, hreg); // row of h: 64 fp16 = 32 columns
+                tmem_st32(tmem_base + lane_taddr + (unit_no % kT16aTiles) * 64u, hreg);       // row of h: 64 fp16 = 32 columns
+                tmem_st32(tmem_base + lane_taddr + (unit_no % kT16aTiles) * 64u + 32u, lreg); // row of l beside it
                 asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
                 // generic-proxy writes must be visible to the tensor core (async proxy) before it is told
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

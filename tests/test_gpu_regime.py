@@ -659,9 +659,10 @@ def test_every_route_boundary_meets_its_bar(ctx, lwc, oracle, shape):
 @pytest.mark.parametrize("shape", [(600, 128, 3072, 16), (301, 100, 2336, 5), (333, 57, 1024, 3), (2, 64, 96, 16)],
                          ids=lambda s: "R%d_N%d_D%d_M%d" % s)
 def test_operand_a_in_tensor_memory_and_in_shared_memory_agree(lwc, oracle, shape):
-    """The fp32-grade tcgen05 route takes its A operand (the h tile) from TMEM by default (score_tc16a.cuh: the transform
-    warps store it there, one thread per row) and from shared memory under LWC_TC16_A=smem (score_tc16.cuh).  Same pieces,
-    same X chunks; Y runs through one accumulator instead of two, so the last bits may differ -- both meet the bar."""
+    """The fp32-grade tcgen05 route takes its A operands (h for X, l for Y = l h^T) from TMEM by default (score_tc16a.cuh:
+    the transform warps store them there, one thread per row) and both operands from shared memory under LWC_TC16_A=smem
+    (score_tc16.cuh, Y = h l^T).  Same pieces, same X chunks; Y is the transpose and runs through one accumulator instead
+    of two, so the last bits may differ -- both meet the bar."""
     R, N, D, M = shape
     E, V, w = fast_batch(R, N, D, M, seed=1200 + N + D)
     if R > 8:
