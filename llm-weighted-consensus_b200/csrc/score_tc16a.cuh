@@ -16,8 +16,8 @@
 // Measured (same box, LWC_TC16_A=smem against the default): cfg4 2.422 -> 2.349 ms (0.830 -> 0.856 of HBM); 1.6 GB
 // launches: 128 candidates 0.802 -> 0.852, two 64-candidate requests per tile 0.875 -> 0.927, two 48-candidate 0.727 ->
 // 0.762.  With only h moved to TMEM (l still a second B tile in shared memory, 128 KB per unit) the steps were 2.525 ->
-// 2.485 ms, 0.778 -> 0.814, 0.838 -> 0.868; ncu on the 2,048-request slice of that form: 646 -> 601 us, arbitration
-// conflicts on the LSU's shared-memory wavefronts 23 M -> 11 M (profiles/r2_tc16a_raw.csv).  Tried and dropped
+// 2.485 ms, 0.778 -> 0.814, 0.838 -> 0.868.  ncu on the 2,048-request slice (profiles/r2_tc16a_raw.csv): 646 -> 602 us,
+// LSU shared-memory wavefronts 49.7 % -> 37.2 % of the pipe, arbitration conflicts on them 23 M -> 9.8 M.  Tried and dropped
 // (LWC_T16A_SETS=2): a second set of four transform warps taking the odd units -- no gain with two requests per tile, and
 // at 448 threads the 128-register cap spills the one-request epilogue (2.75 ms).
 #pragma once
