@@ -19,7 +19,10 @@
 // 2.485 ms, 0.778 -> 0.814, 0.838 -> 0.868.  ncu on the 2,048-request slice (profiles/r2_tc16a_raw.csv): 646 -> 602 us,
 // LSU shared-memory wavefronts 49.7 % -> 37.2 % of the pipe, arbitration conflicts on them 23 M -> 9.8 M.  Tried and dropped
 // (LWC_T16A_SETS=2): a second set of four transform warps taking the odd units -- no gain with two requests per tile, and
-// at 448 threads the 128-register cap spills the one-request epilogue (2.75 ms).
+// at 448 threads the 128-register cap spills the one-request epilogue (2.75 ms).  Also tried and dropped: TMA boxes, MMA
+// width and ring stages sized to the pool (a 96-candidate tile three quarters as tall, 8 stages instead of 6) -- 65..112
+// candidates stayed where they were (80: 0.666, 96: 0.706 of HBM): a tile costs ~0.7-0.9 us per 64-column unit almost
+// regardless of its height, so the limit there is a per-unit latency chain, not bytes through any pipe.
 #pragma once
 
 #include "score_tc16.cuh"
