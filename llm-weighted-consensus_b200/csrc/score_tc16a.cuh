@@ -23,6 +23,11 @@
 // width and ring stages sized to the pool (a 96-candidate tile three quarters as tall, 8 stages instead of 6) -- 65..112
 // candidates stayed where they were (80: 0.666, 96: 0.706 of HBM): a tile costs ~0.7-0.9 us per 64-column unit almost
 // regardless of its height, so the limit there is a per-unit latency chain, not bytes through any pipe.
+// Timing probes on cfg4 (results deliberately wrong, same box, 2.48 ms for the real kernel): without the Y product -- half
+// the MMAs and half the B reads -- 2.21 ms (0.91 of HBM); with ONE [h | l] tile pair in TMEM instead of two
+// (LWC_T16A_TILES=1: the transform may not run ahead of the MMAs at all) 2.49 ms against 2.44.  So what is left is the
+// tensor core's B reads contending with the transform for the shared-memory pipe, not the hand-offs: the next step has
+// to take bytes off that pipe again (the fp32 rows reaching registers without passing through shared memory).
 #pragma once
 
 #include "score_tc16.cuh"
@@ -30,7 +35,10 @@
 namespace lwc {
 
 constexpr uint32_t kT16aCol = 384;  // first TMEM column of the A tiles
-constexpr uint32_t kT16aTiles = 2;  // A tile pairs in flight: [h | l] of one unit, 32 + 32 columns
+#ifndef LWC_T16A_TILES
+#define LWC_T16A_TILES 2
+#endif
+constexpr uint32_t kT16aTiles = LWC_T16A_TILES;  // A tile pairs in flight: [h | l] of one unit, 32 + 32 columns
 #ifndef LWC_T16A_SETS
 #define LWC_T16A_SETS 1
 #endif
