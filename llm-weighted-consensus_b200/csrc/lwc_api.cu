@@ -321,7 +321,8 @@ cudaError_t ensure_fix_flags(lwc_ctx *ctx, int R) {
 }
 
 // list != nullptr: one launch over a list of same-shaped batches (score_stream_list_kernel); p.R = all requests of the list
-template <int NT, bool X3, int NCW, int NF, int NB = NT / 8>
+// GROUP: 8 / N requests of at most 4 candidates share one 8-row tile of the half-tile form (score_stream.cuh)
+template <int NT, bool X3, int NCW, int NF, int NB = NT / 8, bool GROUP = false>
 cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t st, const lwc::ScoreList *list = nullptr) {
     using C = lwc::StreamCfg<NT, X3, NCW, NF>;
     lwc::StreamGeom geo;
@@ -346,15 +347,17 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
     if (geo.stages < 1) return cudaErrorInvalidConfiguration;
     static std::atomic<bool> configured[64]; // zero-initialised; set once per device (contexts on other threads may race here)
     if (!configured[ctx->device & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(lwc::score_stream_kernel<NT, X3, NCW, NF, NB>,
+        cudaError_t e = cudaFuncSetAttribute(lwc::score_stream_kernel<NT, X3, NCW, NF, NB, GROUP>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->max_smem_optin);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(lwc::score_stream_list_kernel<NT, X3, NCW, NF, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            e = cudaFuncSetAttribute(lwc::score_stream_list_kernel<NT, X3, NCW, NF, NB, GROUP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      ctx->max_smem_optin);
         if (e != cudaSuccess) return e;
         configured[ctx->device & 63] = true;
     }
-    const int grid = p.R < ctx->sm_count ? p.R : ctx->sm_count;
+    const int per_tile = GROUP ? 8 / p.N : 1;
+    const int ntiles = (p.R + per_tile - 1) / per_tile;
+    const int grid = ntiles < ctx->sm_count ? ntiles : ctx->sm_count;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(C::THREADS);
@@ -365,8 +368,8 @@ cudaError_t launch_stream_one(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStrea
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (list) return cudaLaunchKernelEx(&cfg, lwc::score_stream_list_kernel<NT, X3, NCW, NF, NB>, p, geo, *list);
-    return cudaLaunchKernelEx(&cfg, lwc::score_stream_kernel<NT, X3, NCW, NF, NB>, p, geo);
+    if (list) return cudaLaunchKernelEx(&cfg, lwc::score_stream_list_kernel<NT, X3, NCW, NF, NB, GROUP>, p, geo, *list);
+    return cudaLaunchKernelEx(&cfg, lwc::score_stream_kernel<NT, X3, NCW, NF, NB, GROUP>, p, geo);
 }
 
 template <int NT, bool X3>
@@ -374,6 +377,9 @@ cudaError_t launch_stream(lwc_ctx *ctx, const lwc::ScoreParams &p, cudaStream_t 
     const int ncw = ctx->stream_ncw ? ctx->stream_ncw : (NT == 16 ? 12 : 8);
     const int nf = ctx->stream_nf ? ctx->stream_nf : (NT == 16 ? 4 : 2);
     // pools of at most 8 candidates: the half-tile form (score_stream.cuh, NB = 1); LWC_STREAM_HALF=0 keeps the full tile
+    // at most 4 candidates: 8 / N requests per tile of that form; LWC_STREAM_GROUP=0 keeps one
+    if (NT == 16 && p.N <= 4 && !ctx->stream_no_half && !ctx->stream_no_group && ncw == 12 && nf == 4)
+        return launch_stream_one<16, X3, 12, 4, 1, true>(ctx, p, st);
     if (NT == 16 && p.N <= 8 && !ctx->stream_no_half && ncw == 12 && nf == 4) return launch_stream_one<16, X3, 12, 4, 1>(ctx, p, st);
     if (NT == 32 && p.N <= 24 && !ctx->stream_no_half && ncw == 8 && nf == 2) return launch_stream_one<32, X3, 8, 2, 3>(ctx, p, st);
     switch (ncw * 10 + nf) {
@@ -419,11 +425,13 @@ SmallRoute small_route(const lwc_ctx *ctx, const Plan &pl) {
         // stage, parks, a finaliser drains), the direct kernel a CTA launch.  Measured crossover (profiles/
         // r2_width_sweep.jsonl): 16 x 384 runs at 0.78 of HBM direct against 0.49 on the ring, 16 x 768 at 0.86 / 0.82,
         // 16 x 1536 (cfg2) at 0.93 / 1.00.  LWC_SMALL_IMPL=stream keeps the ring for everything.
+        // (at most 4 candidates: 8 / N requests share a tile and the ring is kept down to 5 KB per tile -- 3 x 768 runs at
+        // 0.50 of HBM there, 0.24 one CTA per request; 3 x 384 at 0.17 one CTA per request)
         // Pools of at most 8 candidates keep the ring down to 20 KB (its half-tile form does half the work per byte;
         // 8 x 1024 runs at 0.74 there against 0.61 direct), single-pass TF32 down to 40 KB (16 x 768: 1.00 / 0.96).
         // 9..12 candidates, fp32-grade: the ring does a full 16-row tile's work for them at any width (10 x 1536: 0.63 of
         // HBM, compute-bound like 16 x 1536) -- direct at every size (0.75-0.77; 12: 0.80-0.85 against 0.75-0.84).
-        r.stream = !(pl.x3 && pl.n >= 9 && pl.n <= 12) && pl.req_bytes > (pl.n <= 8 ? kDirectBelowBytes8 : (pl.np == 32 ? kDirectBelowBytes32 : (pl.x3 ? kDirectBelowBytes : kDirectBelowBytesTf32)));
+        r.stream = !(pl.x3 && pl.n >= 9 && pl.n <= 12) && pl.req_bytes * (pl.n >= 1 && pl.n <= 4 && !ctx->stream_no_group ? 4 * (8 / pl.n) : 1) > (pl.n <= 8 ? kDirectBelowBytes8 : (pl.np == 32 ? kDirectBelowBytes32 : (pl.x3 ? kDirectBelowBytes : kDirectBelowBytesTf32)));
     r.f16 = f16_ok && !r.stream;
     return r;
 }
@@ -435,7 +443,9 @@ bool list_route(const lwc_ctx *ctx, const Plan &pl) {
 }
 int launch_list(lwc_ctx *ctx, const Plan &pl, const lwc::ScoreParams &p, const lwc::ScoreList &list, cudaStream_t st) {
     cudaError_t e;
-    if (pl.np == 16 && p.N <= 8 && !ctx->stream_no_half)
+    if (pl.np == 16 && p.N <= 4 && !ctx->stream_no_half && !ctx->stream_no_group && list.R_each % (8 / p.N) == 0)
+        e = pl.x3 ? launch_stream_one<16, true, 12, 4, 1, true>(ctx, p, st, &list) : launch_stream_one<16, false, 12, 4, 1, true>(ctx, p, st, &list);
+    else if (pl.np == 16 && p.N <= 8 && !ctx->stream_no_half)
         e = pl.x3 ? launch_stream_one<16, true, 12, 4, 1>(ctx, p, st, &list) : launch_stream_one<16, false, 12, 4, 1>(ctx, p, st, &list);
     else if (pl.np == 16)
         e = pl.x3 ? launch_stream_one<16, true, 12, 4>(ctx, p, st, &list) : launch_stream_one<16, false, 12, 4>(ctx, p, st, &list);
@@ -753,6 +763,7 @@ int32_t lwc_ctx_create(const lwc_config *cfg, lwc_ctx **out) {
     if (const char *s = getenv("LWC_TC_PAIR")) ctx->tc_no_pair = atoi(s) == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_TC16_A")) ctx->tc16_a_tmem = strcmp(s, "tmem") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_STREAM_HALF")) ctx->stream_no_half = atoi(s) == 0 ? 1 : 0;
+    if (const char *s = getenv("LWC_STREAM_GROUP")) ctx->stream_no_group = atoi(s) == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_X3")) ctx->small_x3_tf32 = strcmp(s, "tf32") == 0 ? 1 : 0;
     if (const char *s = getenv("LWC_SMALL_PIPE")) ctx->small_pipe = atoi(s);
     if (const char *s = getenv("LWC_SMALL_ZERO_COPY")) ctx->small_zero_copy = atoi(s);

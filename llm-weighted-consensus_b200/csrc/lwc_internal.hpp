@@ -76,6 +76,7 @@ struct lwc_ctx {
     int small_pipe = 3;        // LWC_SMALL_PIPE=0|3|4: shared-memory load pipeline stages of the 32-row fp16-piece kernel (0: register loads)
     int small_x3_tf32 = 0;     // LWC_SMALL_X3=tf32: the one-CTA-per-request fp32-grade kernel on tf32 pieces
     int stream_parks = 0;      // LWC_STREAM_PARKS=1|2: park buffers of the ring kernel (0: by request size)
+    int stream_no_group = 0;   // LWC_STREAM_GROUP=0: pools of <= 4 candidates one to an 8-row tile of the ring kernel
     int stream_no_half = 0;    // LWC_STREAM_HALF=0: pools of <= 8 candidates on the full 16-row tile of the ring kernel
     int tc16_a_tmem = 1;       // LWC_TC16_A=tmem|smem: fp32-grade tcgen05 route with the A operand in tensor memory (score_tc16a.cuh)
     int tc_no_pair = 0;        // LWC_TC_PAIR=0: pools of <= 64 candidates one to a tile (score_tc16_kernel<false>)

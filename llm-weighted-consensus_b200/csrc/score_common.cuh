@@ -201,6 +201,106 @@ __device__ __forceinline__ void warp_tally_and_rank_pf(const ScoreParams &p, int
     }
 }
 
+// The same tail for a GROUP of G = 8 / N requests of at most 4 candidates each whose rows share one 8-row Gram tile:
+// lane l < G * N owns choice l % N of request r0 + l / N.  S holds the 8 x 8 Gram matrix of the stacked rows; only its
+// diagonal N x N blocks mean anything (the others are products across requests) and every sum below runs over the
+// lane's own block -- in the order warp_sum's butterfly adds four leading lanes, (v0 + v2) + (v1 + v3), so that a request
+// gets the bits it would get alone in a tile.  n_valid: requests of the group that exist (the last group of a batch may
+// be short; rows of absent requests hold stale data that is never selected into a sum).  The first MU voters' entries
+// arrive prefetched: pv[m] = V[r][m][c], pw[m] = w[r][m] of the lane's own request.
+__device__ __forceinline__ float block_sum4(float x, int first, int N) {
+    float a[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float v = __shfl_sync(kFullMask, x, (first + k) & 31);
+        a[k] = k < N ? v : 0.f;
+    }
+    return (a[0] + a[2]) + (a[1] + a[3]);
+}
+
+template <int MU>
+__device__ __forceinline__ void warp_tally_group(const ScoreParams &p, int r0, int G, int n_valid, const float *S, int pitch,
+                                                 int lane, const float *pv, const float *pw) {
+    const int N = p.N, M = p.M;
+    const int g = lane / N, c = lane - g * N; // (N <= 4: a handful of integer ops)
+    const bool act = lane < G * N && g < n_valid;
+    const int r = r0 + (act ? g : 0);
+    const int first = act ? g * N : 0; // lane of the block's choice 0
+    const float *Vr = p.V + (size_t)r * M * N;
+    const float *wr = p.w + (p.w_per_request ? (size_t)r * M : 0);
+
+    float t = 0.f;
+#pragma unroll
+    for (int m = 0; m < MU; ++m) {
+        if (m < M) {
+            const float v0 = __shfl_sync(kFullMask, pv[m], first);
+            float wm = pw[m];
+            if (isnan(wm)) wm = 0.f;
+            if (!isnan(v0) && act) t = fmaf(pv[m], wm, t);
+        }
+    }
+    for (int m = MU; m < M; ++m) { // (few candidates: the voters beyond the prefetch window one at a time)
+        const float v0 = act ? __ldg(Vr + (size_t)m * N) : __int_as_float(0x7fc00000);
+        float wm = act ? __ldg(wr + m) : 0.f;
+        const float vl = act ? __ldg(Vr + (size_t)m * N + c) : 0.f;
+        if (isnan(wm)) wm = 0.f;
+        if (!isnan(v0)) t = fmaf(vl, wm, t);
+    }
+
+    float cwv = t;
+    if (p.cosine) {
+        const int jl = act ? lane : 0;
+        const float d = act ? S[jl * pitch + jl] : 0.f;
+        const float rn = d > 0.f ? 1.0f / sqrtf(d) : 0.f;
+        const float u = t * rn;
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { // own block only, ascending like the single-request loop
+            const float uk = __shfl_sync(kFullMask, u, (first + k) & 31);
+            if (k < N) acc = fmaf(uk, S[(first + k) * pitch + jl], acc);
+        }
+        cwv = acc * rn;
+    }
+    if (!act) cwv = 0.f;
+    const float sum = block_sum4(cwv, first, N);
+    const bool positive = sum > 0.f;
+    const float cf = (positive && act) ? cwv / sum : 0.f;
+    if (act) {
+        if (p.cw) p.cw[(size_t)r * N + c] = cwv;
+        if (p.conf) p.conf[(size_t)r * N + c] = cf;
+    }
+    // argmax (ties -> lowest index) and rank inside the block
+    float best = -1.f;
+    int besti = 0, pos = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float ck = __shfl_sync(kFullMask, cf, (first + k) & 31);
+        if (k < N) {
+            if (ck > best) best = ck, besti = k;
+            pos += (ck > cf || (ck == cf && k < c)) ? 1 : 0;
+        }
+    }
+    if (act) {
+        if (p.winner && c == 0) p.winner[r] = positive ? besti : -1;
+        if (p.rank) p.rank[(size_t)r * N + pos] = c;
+    }
+    if (p.agree) {
+#pragma unroll
+        for (int m = 0; m < MU; ++m) {
+            if (m < M) {
+                const float a = block_sum4(act ? cf * pv[m] : 0.f, first, N);
+                const float v0 = __shfl_sync(kFullMask, pv[m], first);
+                if (act && c == 0) p.agree[(size_t)r * M + m] = isnan(v0) ? __int_as_float(0x7fc00000) : a;
+            }
+        }
+        for (int m = MU; m < M; ++m) {
+            const float v0 = act ? __ldg(Vr + (size_t)m * N) : 0.f;
+            const float a = block_sum4(act ? cf * __ldg(Vr + (size_t)m * N + c) : 0.f, first, N);
+            if (act && c == 0) p.agree[(size_t)r * M + m] = isnan(v0) ? __int_as_float(0x7fc00000) : a;
+        }
+    }
+}
+
 template <int NTP>
 __device__ __forceinline__ void warp_tally_and_rank(const ScoreParams &p, int r, const float *S, int pitch,
                                                     int lane) {

@@ -145,9 +145,14 @@ __device__ __forceinline__ ScoreParams list_params(const ScoreParams &p, const S
 // the form for pools of at most 8 candidates: rows 8..15 are neither loaded nor multiplied (their A registers are
 // constant zeros), the second column tile is never computed -- half the shared-memory loads, piece splits and MMAs of
 // a request, which is what bounds this kernel when a request brings half the bytes.
-template <int NT, bool X3, int NCW, int NFIN, bool LIST, int NB = NT / 8>
+// GROUP (half-tile form only, N <= 4): G = 8 / N consecutive requests share one 8-row tile.  Their rows are contiguous in
+// E, so producer and consumers treat the group as one request of G * N rows; only the finaliser knows better
+// (warp_tally_group: every sum over the lane's own N x N block of the 8 x 8 Gram matrix).  A 4-candidate pool then costs
+// the consumers half, a 2-candidate pool a quarter, of what it costs alone in a tile.
+template <int NT, bool X3, int NCW, int NFIN, bool LIST, int NB = NT / 8, bool GROUP = false>
 __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const StreamGeom &geo, const ScoreList *list) {
     using C = StreamCfg<NT, X3, NCW, NFIN>;
+    static_assert(!GROUP || NB == 1, "request groups: the half-tile form only");
     constexpr int RPL = C::RPL, MT = C::MT, NF = C::NF;
     constexpr int NTL = NB; // column tiles in use (C::NTL of them have room in the park buffer and the S tile)
     static_assert(NB >= 1 && NB <= C::NTL && (NB == C::NTL || NB == C::NTL - 1), "NB: the full tile or one 8-row group less");
@@ -167,11 +172,14 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
     const uint32_t redfull0 = empty0 + 8 * MAXS, redempty0 = redfull0 + 16, turn0 = redempty0 + 16; // [2] each
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int N = p.N, D = p.D, M = p.M;
-    const int r_begin = (int)(((long long)blockIdx.x * p.R) / gridDim.x);
-    const int r_end = (int)(((long long)(blockIdx.x + 1) * p.R) / gridDim.x);
+    const int D = p.D, M = p.M;
+    const int G = GROUP ? 8 / p.N : 1;    // requests per tile
+    const int N = GROUP ? G * p.N : p.N;  // rows per tile: what the producer copies and the consumers multiply
+    const int ntiles = GROUP ? (p.R + G - 1) / G : p.R;
+    const int r_begin = (int)(((long long)blockIdx.x * ntiles) / gridDim.x); // in tiles
+    const int r_end = (int)(((long long)(blockIdx.x + 1) * ntiles) / gridDim.x);
     const int nreq = r_end - r_begin;
-    const int spr = (D + KS - 1) / KS; // stages per request
+    const int spr = (D + KS - 1) / KS; // stages per tile
 
     // rows >= N are never written by a copy and must read as zeros
     if (N < SROWS) {
@@ -205,19 +213,21 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
         uint32_t phase = 0;
         for (int q = 0; q < nreq; ++q) {
             const float *Er;
+            const int g0 = (r_begin + q) * G; // first request of the tile
             if (LIST) {
                 int rl;
-                const ScoreParams pb = list_params(p, list, r_begin + q, &rl);
-                Er = pb.E + (size_t)rl * N * D;
+                const ScoreParams pb = list_params(p, list, g0, &rl); // (a group never straddles two batches: lwc_api.cu)
+                Er = pb.E + (size_t)rl * p.N * D;
             } else {
-                Er = p.E + (size_t)(r_begin + q) * N * D;
+                Er = p.E + (size_t)g0 * p.N * D;
             }
+            const int rows = GROUP ? min(G, p.R - g0) * p.N : N; // the last group of a batch may be short
             for (int s = 0; s < spr; ++s) {
                 mbar_wait(empty0 + 8 * slot, phase ^ 1u);
                 const int kv = min(KS, D - s * KS);
-                if (lane == 0) mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)(kv * 4 * N));
+                if (lane == 0) mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)(kv * 4 * rows));
                 __syncwarp();
-                if (lane < N)
+                if (lane < rows)
                     bulk_g2s(ring_u32 + slot * stageb + lane * pitchb, Er + (size_t)lane * D + (size_t)s * KS,
                              (uint32_t)(kv * 4), full0 + 8 * slot);
                 if (++slot == S) {
@@ -367,18 +377,23 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
     const int f = warp - 1 - NCW;
     float *tile = tiles + (size_t)f * NT * TPITCH;
     float pv[kVotePrefetch], pw[kVotePrefetch];
-    auto prefetch_votes = [&](int r) {
+    auto prefetch_votes = [&](int r) { // r: tile index (= request index unless GROUP)
         ScoreParams pb = p;
+        const int pn = p.N;
+        const int gl = GROUP ? lane / pn : 0, cl = GROUP ? lane - gl * pn : lane; // this lane's request of the group, choice
+        int rq = r * G;
+        const bool ok = GROUP ? (lane < G * pn && rq + gl < p.R) : lane < pn;
         if (LIST) {
-            const int g = r;
-            pb = list_params(p, list, g, &r);
+            const int g = rq;
+            pb = list_params(p, list, g, &rq);
         }
-        const float *Vr = pb.V + (size_t)r * M * N;
-        const float *wr = pb.w + (pb.w_per_request ? (size_t)r * M : 0);
+        rq += ok ? gl : 0;
+        const float *Vr = pb.V + (size_t)rq * M * pn;
+        const float *wr = pb.w + (pb.w_per_request ? (size_t)rq * M : 0);
 #pragma unroll
         for (int m = 0; m < kVotePrefetch; ++m) {
-            pv[m] = (m < M && lane < N) ? __ldg(Vr + (size_t)m * N + lane) : 0.f;
-            pw[m] = (m < M) ? __ldg(wr + m) : 0.f;
+            pv[m] = (m < M && ok) ? __ldg(Vr + (size_t)m * pn + cl) : 0.f;
+            pw[m] = (m < M && (ok || !GROUP)) ? __ldg(wr + m) : 0.f;
         }
     };
     if (f < nreq) prefetch_votes(r_begin + f);
@@ -454,7 +469,16 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
                     }
                 }
         __syncwarp();
-        if (LIST) {
+        if (GROUP) {
+            const int g0 = r * G, nv = min(G, p.R - g0);
+            if (LIST) {
+                int rl;
+                const ScoreParams pb = list_params(p, list, g0, &rl);
+                warp_tally_group<kVotePrefetch>(pb, rl, G, nv, tile, TPITCH, lane, pv, pw);
+            } else {
+                warp_tally_group<kVotePrefetch>(p, g0, G, nv, tile, TPITCH, lane, pv, pw);
+            }
+        } else if (LIST) {
             int rl;
             const ScoreParams pb = list_params(p, list, r, &rl);
             warp_tally_and_rank_pf<kVotePrefetch, NB * 8>(pb, rl, tile, TPITCH, lane, pv, pw);
@@ -466,17 +490,17 @@ __device__ __forceinline__ void score_stream_body(const ScoreParams &p, const St
     }
 }
 
-template <int NT, bool X3, int NCW, int NFIN, int NB = NT / 8>
+template <int NT, bool X3, int NCW, int NFIN, int NB = NT / 8, bool GROUP = false>
 __global__ void __launch_bounds__((1 + NCW + NFIN) * 32, 1)
 score_stream_kernel(const ScoreParams p, const StreamGeom geo) {
-    score_stream_body<NT, X3, NCW, NFIN, false, NB>(p, geo, nullptr);
+    score_stream_body<NT, X3, NCW, NFIN, false, NB, GROUP>(p, geo, nullptr);
 }
 
 // p.R = list.n * list.R_each; p's own pointers are unused
-template <int NT, bool X3, int NCW, int NFIN, int NB = NT / 8>
+template <int NT, bool X3, int NCW, int NFIN, int NB = NT / 8, bool GROUP = false>
 __global__ void __launch_bounds__((1 + NCW + NFIN) * 32, 1)
 score_stream_list_kernel(const ScoreParams p, const StreamGeom geo, const __grid_constant__ ScoreList list) {
-    score_stream_body<NT, X3, NCW, NFIN, true, NB>(p, geo, &list);
+    score_stream_body<NT, X3, NCW, NFIN, true, NB, GROUP>(p, geo, &list);
 }
 
 } // namespace lwc

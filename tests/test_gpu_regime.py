@@ -531,8 +531,8 @@ def test_pools_of_17_to_24_skip_the_fourth_row_group(lwc, oracle, shape, prec):
 
 
 @pytest.mark.parametrize("shape,prec", [((600, 16, 1536, 4), "fp32"), ((450, 32, 1024, 4), "tf32"), ((300, 9, 772, 3), "fp32"), ((500, 6, 1536, 4), "fp32"),
-                                        ((400, 22, 1024, 4), "tf32")],
-                         ids=["cfg2_shape", "n32_tf32", "ragged", "half_tile", "three_groups"])
+                                        ((400, 22, 1024, 4), "tf32"), ((600, 4, 1536, 4), "fp32"), ((501, 3, 1536, 4), "fp32")],
+                         ids=["cfg2_shape", "n32_tf32", "ragged", "half_tile", "three_groups", "grouped", "grouped_odd"])
 def test_a_run_of_same_shaped_batches_is_one_launch_with_the_same_bits(lwc, oracle, shape, prec):
     """lwc_score_batches turns a run of same-shaped ring-kernel batches into ONE launch whose persistent CTAs walk
     the whole run (request g = request g % R of batch g / R).  Launch count, bit-equality with single calls, and
@@ -676,3 +676,30 @@ def test_operand_a_in_tensor_memory_and_in_shared_memory_agree(lwc, oracle, shap
             properties_hold(res[a], V)
     assert np.array_equal(res["tmem"]["winner"], res["smem"]["winner"])
     np.testing.assert_allclose(res["tmem"]["conf"], res["smem"]["conf"], rtol=2e-5, atol=2e-7)  # each within 1e-5 + 1e-7 of the oracle
+
+
+@pytest.mark.parametrize("shape", [(701, 4, 1536, 4), (300, 3, 100, 3), (7, 1, 64, 1), (903, 2, 3072, 0), (450, 4, 772, 9), (1, 2, 32, 2)],
+                         ids=lambda s: "R%d_N%d_D%d_M%d" % s)
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_pools_of_at_most_four_share_a_tile(lwc, oracle, shape, prec):
+    """N <= 4 on the ring kernel: 8 / N consecutive requests share one 8-row tile (their rows are contiguous in E); the
+    finaliser tallies every request over its own N x N block of the 8 x 8 Gram matrix (warp_tally_group), adding in the
+    order the single-request tail does.  Bit-equal to one request per tile (LWC_STREAM_GROUP=0), also for the short last
+    group of an odd batch, and within the route's bar against the oracle."""
+    R, N, D, M = shape
+    p = lwc.PREC_FP32 if prec == "fp32" else lwc.PREC_TF32
+    E, V, w = fast_batch(R, N, D, max(M, 1), seed=1300 + N + D)
+    if M == 0:
+        V, w = V[:, :0], w[:, :0]
+    res = {}
+    for grp in ("1", "0"):
+        with env(LWC_STREAM_GROUP=grp, LWC_SMALL_IMPL="stream"), lwc.Context(device=0) as c:
+            res[grp] = c.score_batch_device(E, V, w, precision=p)
+    for k in res["1"]:
+        assert np.array_equal(res["1"][k], res["0"][k], equal_nan=True), k
+    want = oracle.score_f64(E, V, w, oracle.SIM_COSINE)
+    if prec == "fp32":
+        assert compare(res["1"], want, V) == 1.0
+    else:
+        compare(res["1"], want, V, rtol=TF32_RTOL, atol=1e-5, gap=5e-3, min_agreement=0.95, atol_of_max=TF32_RTOL)
+    properties_hold(res["1"], V)
